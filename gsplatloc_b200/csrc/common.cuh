@@ -1,0 +1,230 @@
+// Shared device math for the GsplatLoc hot path on sm_100a.
+// Semantics follow SURVEY.md Appendix A (gsplat 1.3.0 as called from src/my_gsplat/model.py:195-213).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define GSB_TILE 16                  // reference default tile_size (Appendix A.1); raster kernels are built for it
+#define GSB_ALPHA_MIN (1.f / 255.f)  // A.4 skip threshold
+#define GSB_ALPHA_MAX 0.999f         // A.4 alpha clamp
+#define GSB_T_STOP 1e-4f             // A.4 stop threshold
+
+namespace gsb {
+
+struct Cam {
+    float R[9];  // world->camera rotation, row-major
+    float t[3];
+    float fx, fy, cx, cy;
+};
+
+__device__ __forceinline__ Cam load_cam(const float* __restrict__ viewmat, const float* __restrict__ K) {
+    Cam c;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+#pragma unroll
+        for (int j = 0; j < 3; ++j) c.R[i * 3 + j] = viewmat[i * 4 + j];
+        c.t[i] = viewmat[i * 4 + 3];
+    }
+    c.fx = K[0]; c.cx = K[2]; c.fy = K[4]; c.cy = K[5];
+    return c;
+}
+
+// wxyz quaternion (normalised here) -> row-major rotation (A.6 matrix; same as gsplat quat_to_rotmat)
+__device__ __forceinline__ void quat_to_rotmat(float w, float x, float y, float z, float* __restrict__ R) {
+    float inv = rsqrtf(w * w + x * x + y * y + z * z);
+    w *= inv; x *= inv; y *= inv; z *= inv;
+    float x2 = x * x, y2 = y * y, z2 = z * z, xy = x * y, xz = x * z, yz = y * z, wx = w * x, wy = w * y, wz = w * z;
+    R[0] = 1.f - 2.f * (y2 + z2); R[1] = 2.f * (xy - wz);       R[2] = 2.f * (xz + wy);
+    R[3] = 2.f * (xy + wz);       R[4] = 1.f - 2.f * (x2 + z2); R[5] = 2.f * (yz - wx);
+    R[6] = 2.f * (xz - wy);       R[7] = 2.f * (yz + wx);       R[8] = 1.f - 2.f * (x2 + y2);
+}
+
+// Sigma = (Rq diag(s)) (Rq diag(s))^T, symmetric storage [00,01,02,11,12,22]
+__device__ __forceinline__ void quat_scale_to_covar(const float* __restrict__ q, const float* __restrict__ s,
+                                                    float* __restrict__ S) {
+    float R[9];
+    quat_to_rotmat(q[0], q[1], q[2], q[3], R);
+    float M[9];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) M[i * 3 + j] = R[i * 3 + j] * s[j];
+    S[0] = M[0] * M[0] + M[1] * M[1] + M[2] * M[2];
+    S[1] = M[0] * M[3] + M[1] * M[4] + M[2] * M[5];
+    S[2] = M[0] * M[6] + M[1] * M[7] + M[2] * M[8];
+    S[3] = M[3] * M[3] + M[4] * M[4] + M[5] * M[5];
+    S[4] = M[3] * M[6] + M[4] * M[7] + M[5] * M[8];
+    S[5] = M[6] * M[6] + M[7] * M[7] + M[8] * M[8];
+}
+
+// Sc = R S R^T for symmetric S (6) -> symmetric Sc (6)
+__device__ __forceinline__ void covar_world_to_cam(const float* __restrict__ R, const float* __restrict__ S,
+                                                   float* __restrict__ Sc) {
+    float A[9];  // A = R S
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        float r0 = R[i * 3], r1 = R[i * 3 + 1], r2 = R[i * 3 + 2];
+        A[i * 3 + 0] = r0 * S[0] + r1 * S[1] + r2 * S[2];
+        A[i * 3 + 1] = r0 * S[1] + r1 * S[3] + r2 * S[4];
+        A[i * 3 + 2] = r0 * S[2] + r1 * S[4] + r2 * S[5];
+    }
+    Sc[0] = A[0] * R[0] + A[1] * R[1] + A[2] * R[2];
+    Sc[1] = A[0] * R[3] + A[1] * R[4] + A[2] * R[5];
+    Sc[2] = A[0] * R[6] + A[1] * R[7] + A[2] * R[8];
+    Sc[3] = A[3] * R[3] + A[4] * R[4] + A[5] * R[5];
+    Sc[4] = A[3] * R[6] + A[4] * R[7] + A[5] * R[8];
+    Sc[5] = A[6] * R[6] + A[7] * R[7] + A[8] * R[8];
+}
+
+struct Proj {
+    float px, py, pz;      // camera-space mean
+    float mx, my;          // 2-D mean
+    float ca, cb, cc;      // conic
+    float j00, j11, j02, j12, rz, tx, ty;
+    bool in_x, in_y;       // inside the 1.3*fov clamp
+    int radius;            // 0 == culled
+};
+
+// A.2 forward for one Gaussian given its camera-space covariance Sc.
+__device__ __forceinline__ void persp_project(const Cam& cam, const float* __restrict__ Sc, int W, int H,
+                                              float eps2d, float radius_clip, Proj& p) {
+    float x = p.px, y = p.py, z = p.pz;
+    float limx = 1.3f * (0.5f * W / cam.fx), limy = 1.3f * (0.5f * H / cam.fy);
+    float rz = 1.f / z, rz2 = rz * rz;
+    float xr = x * rz, yr = y * rz;
+    p.in_x = (xr <= limx) && (xr >= -limx);
+    p.in_y = (yr <= limy) && (yr >= -limy);
+    float tx = z * fminf(limx, fmaxf(-limx, xr));
+    float ty = z * fminf(limy, fmaxf(-limy, yr));
+    float j00 = cam.fx * rz, j11 = cam.fy * rz, j02 = -cam.fx * tx * rz2, j12 = -cam.fy * ty * rz2;
+    p.rz = rz; p.tx = tx; p.ty = ty; p.j00 = j00; p.j11 = j11; p.j02 = j02; p.j12 = j12;
+    float c00 = j00 * j00 * Sc[0] + 2.f * j00 * j02 * Sc[2] + j02 * j02 * Sc[5];
+    float c01 = j00 * j11 * Sc[1] + j00 * j12 * Sc[2] + j02 * j11 * Sc[4] + j02 * j12 * Sc[5];
+    float c11 = j11 * j11 * Sc[3] + 2.f * j11 * j12 * Sc[4] + j12 * j12 * Sc[5];
+    p.mx = cam.fx * x * rz + cam.cx;
+    p.my = cam.fy * y * rz + cam.cy;
+    c00 += eps2d; c11 += eps2d;
+    float det = c00 * c11 - c01 * c01;
+    p.radius = 0;
+    if (det <= 0.f) return;
+    float idet = 1.f / det;
+    p.ca = c11 * idet; p.cb = -c01 * idet; p.cc = c00 * idet;
+    float b = 0.5f * (c00 + c11);
+    float v1 = b + sqrtf(fmaxf(0.01f, b * b - det));
+    float radius = ceilf(3.f * sqrtf(v1));
+    if (radius <= radius_clip) return;
+    if (p.mx + radius <= 0.f || p.mx - radius >= (float)W || p.my + radius <= 0.f || p.my - radius >= (float)H) return;
+    p.radius = (int)radius;
+}
+
+// Full A.2 for one Gaussian. Returns false when culled (radius 0). S (world covariance) and Sc are returned
+// for the backward lift.
+__device__ __forceinline__ bool project_gaussian(const Cam& cam, const float* __restrict__ mean,
+                                                 const float* __restrict__ quat, const float* __restrict__ scale,
+                                                 int W, int H, float eps2d, float near_plane, float far_plane,
+                                                 float radius_clip, Proj& p, float* __restrict__ S,
+                                                 float* __restrict__ Sc) {
+    p.px = cam.R[0] * mean[0] + cam.R[1] * mean[1] + cam.R[2] * mean[2] + cam.t[0];
+    p.py = cam.R[3] * mean[0] + cam.R[4] * mean[1] + cam.R[5] * mean[2] + cam.t[1];
+    p.pz = cam.R[6] * mean[0] + cam.R[7] * mean[1] + cam.R[8] * mean[2] + cam.t[2];
+    p.radius = 0;
+    if (p.pz < near_plane || p.pz > far_plane) return false;
+    quat_scale_to_covar(quat, scale, S);
+    covar_world_to_cam(cam.R, S, Sc);
+    persp_project(cam, Sc, W, H, eps2d, radius_clip, p);
+    return p.radius > 0;
+}
+
+// A.3 tile bounding box (fp32 exactly as the reference kernel; (u32) of a negative float saturates to 0).
+__device__ __forceinline__ void tile_bbox(float mx, float my, int radius, int tile_size, int tile_w, int tile_h,
+                                          uint32_t& x0, uint32_t& y0, uint32_t& x1, uint32_t& y1) {
+    float ts = (float)tile_size;
+    float tr = (float)radius / ts;
+    float tx = mx / ts, ty = my / ts;
+    x0 = min(__float2uint_rz(floorf(tx - tr)), (uint32_t)tile_w);   // cvt.rzi.u32.f32 saturates negatives to 0
+    y0 = min(__float2uint_rz(floorf(ty - tr)), (uint32_t)tile_h);
+    x1 = min(__float2uint_rz(ceilf(tx + tr)), (uint32_t)tile_w);
+    y1 = min(__float2uint_rz(ceilf(ty + tr)), (uint32_t)tile_h);
+}
+
+// A.6: lift (v_xy, v_conic, v_depth) of one Gaussian through the projection to the world->camera pose.
+// vR (9, row-major) and vt (3) are ACCUMULATED. Optionally returns v_pc (camera-space mean gradient) and
+// vSc (gradient w.r.t. camera-space covariance, symmetric 3x3 full matrix entries [00,01,02,11,12,22] where the
+// off-diagonal entries hold the gradient of ONE of the two symmetric elements).
+__device__ __forceinline__ void project_vjp(const Cam& cam, const Proj& p, const float* __restrict__ Sc,
+                                            float vx, float vy, float va, float vb, float vc, float vdepth,
+                                            float* __restrict__ v_pc, float* __restrict__ vS) {
+    // conic = inverse(cov2d):  v_cov = -Cinv * v_Cinv * Cinv, v_Cinv = [[va, vb/2],[vb/2, vc]]
+    float a = p.ca, b = p.cb, c = p.cc, hb = 0.5f * vb;
+    float X00 = a * va + b * hb, X01 = a * hb + b * vc, X10 = b * va + c * hb, X11 = b * hb + c * vc;
+    float g00 = -(X00 * a + X01 * b), g01 = -(X00 * b + X01 * c), g11 = -(X10 * b + X11 * c);
+    float j00 = p.j00, j11 = p.j11, j02 = p.j02, j12 = p.j12;
+    // vSc = J^T G J
+    float A00 = j00 * g00, A01 = j00 * g01, A10 = j11 * g01, A11 = j11 * g11;
+    float A20 = j02 * g00 + j12 * g01, A21 = j02 * g01 + j12 * g11;
+    vS[0] = A00 * j00; vS[1] = A01 * j11; vS[2] = A00 * j02 + A01 * j12;
+    vS[3] = A11 * j11; vS[4] = A10 * j02 + A11 * j12; vS[5] = A20 * j02 + A21 * j12;
+    // vJ = 2 G (J Sc)   (only the four non-constant entries)
+    float JS00 = j00 * Sc[0] + j02 * Sc[2], JS02 = j00 * Sc[2] + j02 * Sc[5];
+    float JS10 = j11 * Sc[1] + j12 * Sc[2], JS11 = j11 * Sc[3] + j12 * Sc[4], JS12 = j11 * Sc[4] + j12 * Sc[5];
+    float JS01 = j00 * Sc[1] + j02 * Sc[4];
+    float vJ00 = 2.f * (g00 * JS00 + g01 * JS10);
+    float vJ02 = 2.f * (g00 * JS02 + g01 * JS12);
+    float vJ11 = 2.f * (g01 * JS01 + g11 * JS11);
+    float vJ12 = 2.f * (g01 * JS02 + g11 * JS12);
+    float rz = p.rz, rz2 = rz * rz, rz3 = rz2 * rz, fx = cam.fx, fy = cam.fy;
+    float gx = fx * rz * vx, gy = fy * rz * vy;
+    float gz = -(fx * p.px * vx + fy * p.py * vy) * rz2;
+    if (p.in_x) gx += -fx * rz2 * vJ02; else gz += -fx * rz3 * vJ02 * p.tx;
+    if (p.in_y) gy += -fy * rz2 * vJ12; else gz += -fy * rz3 * vJ12 * p.ty;
+    gz += -fx * rz2 * vJ00 - fy * rz2 * vJ11 + 2.f * fx * p.tx * rz3 * vJ02 + 2.f * fy * p.ty * rz3 * vJ12;
+    gz += vdepth;
+    v_pc[0] = gx; v_pc[1] = gy; v_pc[2] = gz;
+}
+
+// v_R += v_pc mean^T + 2 vSc R S ; v_t += v_pc      (S = world covariance, symmetric 6)
+__device__ __forceinline__ void pose_accumulate(const Cam& cam, const float* __restrict__ mean,
+                                                const float* __restrict__ S, const float* __restrict__ v_pc,
+                                                const float* __restrict__ vS, float* __restrict__ vR,
+                                                float* __restrict__ vt) {
+    // B = R S (3x3)
+    float B[9];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        float r0 = cam.R[i * 3], r1 = cam.R[i * 3 + 1], r2 = cam.R[i * 3 + 2];
+        B[i * 3 + 0] = r0 * S[0] + r1 * S[1] + r2 * S[2];
+        B[i * 3 + 1] = r0 * S[1] + r1 * S[3] + r2 * S[4];
+        B[i * 3 + 2] = r0 * S[2] + r1 * S[4] + r2 * S[5];
+    }
+    const float V[9] = {vS[0], vS[1], vS[2], vS[1], vS[3], vS[4], vS[2], vS[4], vS[5]};
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            float acc = V[i * 3] * B[j] + V[i * 3 + 1] * B[3 + j] + V[i * 3 + 2] * B[6 + j];
+            vR[i * 3 + j] += v_pc[i] * mean[j] + 2.f * acc;
+        }
+        vt[i] += v_pc[i];
+    }
+}
+
+// VJP of quat_to_rotmat (incl. the normalisation): vR row-major 9 -> v_quat (wxyz, un-normalised input q)
+__device__ __forceinline__ void quat_to_rotmat_vjp(const float* __restrict__ q, const float* __restrict__ v,
+                                                   float* __restrict__ vq) {
+    float inv = rsqrtf(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+    float w = q[0] * inv, x = q[1] * inv, y = q[2] * inv, z = q[3] * inv;
+    float gw = 2.f * (-z * v[1] + y * v[2] + z * v[3] - x * v[5] - y * v[6] + x * v[7]);
+    float gx = 2.f * (y * v[1] + z * v[2] + y * v[3] - 2.f * x * v[4] - w * v[5] + z * v[6] + w * v[7] - 2.f * x * v[8]);
+    float gy = 2.f * (-2.f * y * v[0] + x * v[1] + w * v[2] + x * v[3] + z * v[5] - w * v[6] + z * v[7] - 2.f * y * v[8]);
+    float gz = 2.f * (-2.f * z * v[0] - w * v[1] + x * v[2] + w * v[3] - 2.f * z * v[4] + y * v[5] + x * v[6] + y * v[7]);
+    float d = gw * w + gx * x + gy * y + gz * z;
+    vq[0] = (gw - d * w) * inv; vq[1] = (gx - d * x) * inv; vq[2] = (gy - d * y) * inv; vq[3] = (gz - d * z) * inv;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+}  // namespace gsb

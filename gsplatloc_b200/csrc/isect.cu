@@ -1,0 +1,331 @@
+// Tile intersection (Appendix A.3).
+//
+// Two routes produce bit-identical (tiles_per_gauss, sorted isect_ids, flatten_ids, offsets):
+//  * "radix": the reference's shape — count, cumsum, emit in index order, one global stable radix sort of the
+//    64-bit cam|tile|depth keys (library sort), boundary scan for the offsets.  Kept as the op-level twin and
+//    as the cross-check of the fast route.
+//  * "tile" (B200-first, used by the tracker): per-tile histogram -> exclusive scan over tiles (this IS the
+//    offsets table) -> scatter (depth|index) into tile bins -> each tile sorts its own bin in shared memory.
+//    A tile holds every Gaussian at most once, so ordering a bin by (depth bits, flat index) reproduces the
+//    global stable sort exactly; no multi-pass sort over all M keys ever touches HBM.
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+#include <cub/iterator/transform_input_iterator.cuh>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace gsb {
+
+// ------------------------------------------------------------------ reference-shaped route
+__global__ void __launch_bounds__(256) isect_count_kernel(int CN, const float* __restrict__ means2d,
+                                                          const int* __restrict__ radii, int tile_size, int tile_w,
+                                                          int tile_h, int* __restrict__ tiles_per_gauss) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= CN) return;
+    int r = radii[i];
+    int cnt = 0;
+    if (r > 0) {
+        uint32_t x0, y0, x1, y1;
+        tile_bbox(means2d[2 * i], means2d[2 * i + 1], r, tile_size, tile_w, tile_h, x0, y0, x1, y1);
+        cnt = (int)((y1 - y0) * (x1 - x0));
+    }
+    tiles_per_gauss[i] = cnt;
+}
+
+__global__ void __launch_bounds__(256) isect_emit_kernel(int CN, int N, const float* __restrict__ means2d,
+                                                         const int* __restrict__ radii,
+                                                         const float* __restrict__ depths,
+                                                         const int64_t* __restrict__ cum, int tile_size, int tile_w,
+                                                         int tile_h, int tile_bits, int64_t* __restrict__ isect_ids,
+                                                         int* __restrict__ flatten_ids) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= CN) return;
+    int r = radii[i];
+    if (r <= 0) return;
+    uint32_t x0, y0, x1, y1;
+    tile_bbox(means2d[2 * i], means2d[2 * i + 1], r, tile_size, tile_w, tile_h, x0, y0, x1, y1);
+    int64_t cid = i / N;
+    int64_t cid_enc = cid << (32 + tile_bits);
+    int64_t depth_enc = (int64_t)__float_as_int(depths[i]);
+    int64_t cur = (i == 0) ? 0 : cum[i - 1];
+    for (uint32_t ty = y0; ty < y1; ++ty)
+        for (uint32_t tx = x0; tx < x1; ++tx) {
+            int64_t tile_id = (int64_t)ty * tile_w + tx;
+            isect_ids[cur] = cid_enc | (tile_id << 32) | depth_enc;
+            flatten_ids[cur] = i;
+            ++cur;
+        }
+}
+
+__global__ void __launch_bounds__(256) offset_encode_kernel(int n_isects, const int64_t* __restrict__ isect_ids,
+                                                            int C, int n_tiles, int tile_bits,
+                                                            int* __restrict__ offsets) {
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n_isects) return;
+    int64_t hi = isect_ids[idx] >> 32;
+    int64_t id_curr = (hi >> tile_bits) * n_tiles + (hi & ((1ll << tile_bits) - 1));
+    if (idx == 0)
+        for (int64_t i = 0; i <= id_curr; ++i) offsets[i] = 0;
+    if (idx == n_isects - 1)
+        for (int64_t i = id_curr + 1; i < (int64_t)C * n_tiles; ++i) offsets[i] = n_isects;
+    if (idx > 0) {
+        int64_t hp = isect_ids[idx - 1] >> 32;
+        if (hp == hi) return;
+        int64_t id_prev = (hp >> tile_bits) * n_tiles + (hp & ((1ll << tile_bits) - 1));
+        for (int64_t i = id_prev + 1; i <= id_curr; ++i) offsets[i] = idx;
+    }
+}
+
+void launch_isect_count(int CN, const float* means2d, const int* radii, int tile_size, int tile_w, int tile_h,
+                        int* tiles_per_gauss, cudaStream_t st) {
+    if (CN == 0) return;
+    isect_count_kernel<<<(CN + 255) / 256, 256, 0, st>>>(CN, means2d, radii, tile_size, tile_w, tile_h,
+                                                         tiles_per_gauss);
+}
+
+size_t cumsum_workspace_bytes(int CN) {
+    size_t bytes = 0;
+    cub::DeviceScan::InclusiveSum((void*)nullptr, bytes, (const int*)nullptr, (int64_t*)nullptr, CN);
+    return bytes;
+}
+
+struct IntToI64 {
+    __host__ __device__ int64_t operator()(int v) const { return (int64_t)v; }
+};
+
+cudaError_t launch_cumsum(int CN, const int* tiles_per_gauss, int64_t* cum, void* ws, size_t ws_bytes,
+                          cudaStream_t st) {
+    if (CN == 0) return cudaSuccess;
+    cub::TransformInputIterator<int64_t, IntToI64, const int*> it(tiles_per_gauss, IntToI64());
+    return cub::DeviceScan::InclusiveSum(ws, ws_bytes, it, cum, CN, st);
+}
+
+void launch_isect_emit(int CN, int N, const float* means2d, const int* radii, const float* depths,
+                       const int64_t* cum, int tile_size, int tile_w, int tile_h, int tile_bits, int64_t* isect_ids,
+                       int* flatten_ids, cudaStream_t st) {
+    if (CN == 0) return;
+    isect_emit_kernel<<<(CN + 255) / 256, 256, 0, st>>>(CN, N, means2d, radii, depths, cum, tile_size, tile_w, tile_h,
+                                                        tile_bits, isect_ids, flatten_ids);
+}
+
+size_t radix_sort_workspace_bytes(int64_t M, int end_bit) {
+    size_t bytes = 0;
+    cub::DeviceRadixSort::SortPairs((void*)nullptr, bytes, (const int64_t*)nullptr, (int64_t*)nullptr,
+                                    (const int*)nullptr, (int*)nullptr, M, 0, end_bit);
+    return bytes;
+}
+
+cudaError_t launch_radix_sort(int64_t M, int end_bit, const int64_t* keys_in, int64_t* keys_out, const int* vals_in,
+                              int* vals_out, void* ws, size_t ws_bytes, cudaStream_t st) {
+    if (M == 0) return cudaSuccess;
+    return cub::DeviceRadixSort::SortPairs(ws, ws_bytes, keys_in, keys_out, vals_in, vals_out, M, 0, end_bit, st);
+}
+
+void launch_offset_encode(int n_isects, const int64_t* isect_ids, int C, int n_tiles, int tile_bits, int* offsets,
+                          cudaStream_t st) {
+    if (n_isects == 0) {
+        cudaMemsetAsync(offsets, 0, sizeof(int) * (size_t)C * n_tiles, st);
+        return;
+    }
+    offset_encode_kernel<<<(n_isects + 255) / 256, 256, 0, st>>>(n_isects, isect_ids, C, n_tiles, tile_bits, offsets);
+}
+
+// ------------------------------------------------------------------ tile-bin route
+// SoA twin of the histogram half of project_bin_kernel, for callers that hold means2d/radii (op-level API).
+__global__ void __launch_bounds__(256) tile_hist_kernel(int CN, int N, const float* __restrict__ means2d,
+                                                        const int* __restrict__ radii, int tile_size, int tile_w,
+                                                        int tile_h, int* __restrict__ tiles_per_gauss,
+                                                        int* __restrict__ counts) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= CN) return;
+    int r = radii[i];
+    int cnt = 0;
+    if (r > 0) {
+        uint32_t x0, y0, x1, y1;
+        tile_bbox(means2d[2 * i], means2d[2 * i + 1], r, tile_size, tile_w, tile_h, x0, y0, x1, y1);
+        cnt = (int)((y1 - y0) * (x1 - x0));
+        int* cb = counts + (size_t)(i / N) * tile_w * tile_h;
+        for (uint32_t ty = y0; ty < y1; ++ty)
+            for (uint32_t tx = x0; tx < x1; ++tx) atomicAdd(cb + ty * tile_w + tx, 1);
+    }
+    if (tiles_per_gauss) tiles_per_gauss[i] = cnt;
+}
+
+// Exclusive scan of the per-(camera,tile) counts by ONE block: offsets[n_bins+1], a cursor copy for the scatter,
+// the total on the device (no host sync) and counts re-zeroed for the next iteration.
+__global__ void __launch_bounds__(1024) tile_scan_kernel(int n_bins, int* __restrict__ counts,
+                                                         int* __restrict__ offsets, int* __restrict__ cursor,
+                                                         int* __restrict__ n_isects, int cap,
+                                                         int* __restrict__ overflow) {
+    __shared__ int warp_tot[32];
+    int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    int per = (n_bins + 1023) / 1024;
+    int lo = min(tid * per, n_bins), hi = min(lo + per, n_bins);
+    int sum = 0;
+    for (int i = lo; i < hi; ++i) sum += counts[i];
+    int inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
+    }
+    if (lane == 31) warp_tot[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        int w = warp_tot[lane], wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int v = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += v;
+        }
+        warp_tot[lane] = wi - w;  // exclusive
+    }
+    __syncthreads();
+    int total_excl = warp_tot[wid] + inc - sum;
+    int run = total_excl;
+    bool over = false;
+    for (int i = lo; i < hi; ++i) {
+        int c = counts[i];
+        counts[i] = 0;
+        offsets[i] = min(run, cap);   // on overflow every range stays inside the buffers (result flagged invalid)
+        cursor[i] = min(run, cap);
+        run += c;
+    }
+    if (tid == 1023) {
+        offsets[n_bins] = min(run, cap);
+        *n_isects = min(run, cap);
+        over = run > cap;
+        if (overflow && over) *overflow = 1;
+    }
+}
+
+// Scatter (depth bits << 32 | flat index) into the tile bins. PACKED: tracker records; else SoA (op-level).
+template <bool PACKED>
+__global__ void __launch_bounds__(256) bin_emit_kernel(int CN, int N, const float4* __restrict__ rec,
+                                                       const uint2* __restrict__ bbox,
+                                                       const float* __restrict__ means2d,
+                                                       const int* __restrict__ radii,
+                                                       const float* __restrict__ depths, int tile_size, int tile_w,
+                                                       int tile_h, int* __restrict__ cursor,
+                                                       uint64_t* __restrict__ keys, int cap,
+                                                       const int* __restrict__ stop) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= CN) return;
+    int c = i / N;
+    if (stop && stop[c]) return;
+    uint32_t x0, y0, x1, y1;
+    float depth;
+    if (PACKED) {
+        uint2 b = bbox[i];
+        x0 = b.x & 0xffffu; x1 = b.x >> 16; y0 = b.y & 0xffffu; y1 = b.y >> 16;
+        if (x1 <= x0 || y1 <= y0) return;
+        depth = rec[2 * (size_t)i].z;
+    } else {
+        int r = radii[i];
+        if (r <= 0) return;
+        tile_bbox(means2d[2 * i], means2d[2 * i + 1], r, tile_size, tile_w, tile_h, x0, y0, x1, y1);
+        depth = depths[i];
+    }
+    uint64_t key = ((uint64_t)(uint32_t)__float_as_int(depth) << 32) | (uint32_t)i;
+    int* cur = cursor + (size_t)c * tile_w * tile_h;
+    for (uint32_t ty = y0; ty < y1; ++ty)
+        for (uint32_t tx = x0; tx < x1; ++tx) {
+            int pos = atomicAdd(cur + ty * tile_w + tx, 1);
+            if (pos < cap) keys[pos] = key;
+        }
+}
+
+// One block per (camera, tile): sort the bin ascending by the unique 64-bit (depth bits, flat index) key.
+// All-ascending bitonic network (flip + disperse); slots >= n behave as +inf and are never touched, so no padding
+// is stored.  Bins that fit SORT_SMEM keys are sorted in shared memory, larger ones in place in global memory.
+#define SORT_SMEM 4096
+__device__ __forceinline__ void cex(uint64_t* a, int x, int y) {
+    uint64_t u = a[x], v = a[y];
+    if (u > v) { a[x] = v; a[y] = u; }
+}
+
+__device__ void bitonic_sort(uint64_t* a, int n) {
+    int P = 1;
+    while (P < n) P <<= 1;
+    for (int h = 2; h <= P; h <<= 1) {
+        int half = h >> 1;
+        for (int t = threadIdx.x; t < (P >> 1); t += blockDim.x) {
+            int q = (t / half) * h, r = t % half;
+            int x = q + r, y = q + h - r - 1;
+            if (y < n) cex(a, x, y);
+        }
+        __syncthreads();
+        for (int hh = half; hh >= 2; hh >>= 1) {
+            int hf = hh >> 1;
+            for (int t = threadIdx.x; t < (P >> 1); t += blockDim.x) {
+                int q = (t / hf) * hh, r = t % hf;
+                int x = q + r, y = x + hf;
+                if (y < n) cex(a, x, y);
+            }
+            __syncthreads();
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) tile_sort_kernel(int n_tiles, int tile_bits, const int* __restrict__ offsets,
+                                                        uint64_t* __restrict__ keys, int* __restrict__ flatten_ids,
+                                                        int64_t* __restrict__ isect_ids, int cap,
+                                                        const int* __restrict__ stop) {
+    __shared__ uint64_t sk[SORT_SMEM];
+    int bin = blockIdx.x;
+    int cam = bin / n_tiles;
+    if (stop && stop[cam]) return;
+    int start = min(offsets[bin], cap), end = min(offsets[bin + 1], cap);
+    int n = end - start;
+    if (n <= 0) return;
+    uint64_t* g = keys + start;
+    uint64_t* a = g;
+    if (n <= SORT_SMEM) {
+        for (int i = threadIdx.x; i < n; i += blockDim.x) sk[i] = g[i];
+        a = sk;
+    }
+    __syncthreads();
+    if (n > 1) bitonic_sort(a, n);
+    int64_t hi = ((int64_t)cam << (32 + tile_bits)) | ((int64_t)(bin % n_tiles) << 32);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        uint64_t k = a[i];
+        flatten_ids[start + i] = (int)(uint32_t)k;
+        if (isect_ids) isect_ids[start + i] = hi | (int64_t)(k >> 32);
+    }
+}
+
+void launch_tile_hist(int CN, int N, const float* means2d, const int* radii, int tile_size, int tile_w, int tile_h,
+                      int* tiles_per_gauss, int* counts, cudaStream_t st) {
+    if (CN == 0) return;
+    tile_hist_kernel<<<(CN + 255) / 256, 256, 0, st>>>(CN, N, means2d, radii, tile_size, tile_w, tile_h,
+                                                       tiles_per_gauss, counts);
+}
+
+void launch_tile_scan(int n_bins, int* counts, int* offsets, int* cursor, int* n_isects, int cap, int* overflow,
+                      cudaStream_t st) {
+    tile_scan_kernel<<<1, 1024, 0, st>>>(n_bins, counts, offsets, cursor, n_isects, cap, overflow);
+}
+
+void launch_bin_emit_packed(int CN, int N, const float4* rec, const uint2* bbox, int tile_w, int tile_h, int* cursor,
+                            uint64_t* keys, int cap, const int* stop, cudaStream_t st) {
+    if (CN == 0) return;
+    bin_emit_kernel<true><<<(CN + 255) / 256, 256, 0, st>>>(CN, N, rec, bbox, nullptr, nullptr, nullptr, GSB_TILE,
+                                                            tile_w, tile_h, cursor, keys, cap, stop);
+}
+
+void launch_bin_emit_soa(int CN, int N, const float* means2d, const int* radii, const float* depths, int tile_size,
+                         int tile_w, int tile_h, int* cursor, uint64_t* keys, int cap, cudaStream_t st) {
+    if (CN == 0) return;
+    bin_emit_kernel<false><<<(CN + 255) / 256, 256, 0, st>>>(CN, N, nullptr, nullptr, means2d, radii, depths,
+                                                             tile_size, tile_w, tile_h, cursor, keys, cap, nullptr);
+}
+
+void launch_tile_sort(int C, int n_tiles, int tile_bits, const int* offsets, uint64_t* keys, int* flatten_ids,
+                      int64_t* isect_ids, int cap, const int* stop, cudaStream_t st) {
+    if (C * n_tiles == 0) return;
+    tile_sort_kernel<<<C * n_tiles, 256, 0, st>>>(n_tiles, tile_bits, offsets, keys, flatten_ids, isect_ids, cap,
+                                                  stop);
+}
+
+}  // namespace gsb

@@ -1,0 +1,88 @@
+// Internal launcher declarations shared by the C-ABI (capi.cu) and the tracker runtime (tracker.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#include "../../include/gsplatloc_b200.h"
+
+namespace gsb {
+
+// ---- projection.cu
+void launch_project_fwd(int C, int N, const float* means, const float* quats, const float* scales,
+                        const float* viewmats, const float* Ks, int W, int H, float eps2d, float near_plane,
+                        float far_plane, float radius_clip, int* radii, float* means2d, float* depths, float* conics,
+                        cudaStream_t st);
+void launch_project_bwd(int C, int N, const float* means, const float* quats, const float* scales,
+                        const float* viewmats, const float* Ks, int W, int H, float eps2d, const int* radii,
+                        const float* v_means2d, const float* v_depths, const float* v_conics, float* v_means,
+                        float* v_quats, float* v_scales, float* v_viewmats, cudaStream_t st);
+void launch_project_bin(int C, int N, const float* means, const float* quats, const float* scales,
+                        const float* opacities, const float* viewmats, const float* Ks, int W, int H, int tile_w,
+                        int tile_h, float eps2d, float near_plane, float far_plane, float radius_clip, float4* rec,
+                        uint2* bbox, int* counts, const int* stop, cudaStream_t st);
+
+// ---- isect.cu
+void launch_isect_count(int CN, const float* means2d, const int* radii, int tile_size, int tile_w, int tile_h,
+                        int* tiles_per_gauss, cudaStream_t st);
+size_t cumsum_workspace_bytes(int CN);
+cudaError_t launch_cumsum(int CN, const int* tiles_per_gauss, int64_t* cum, void* ws, size_t ws_bytes,
+                          cudaStream_t st);
+void launch_isect_emit(int CN, int N, const float* means2d, const int* radii, const float* depths,
+                       const int64_t* cum, int tile_size, int tile_w, int tile_h, int tile_bits, int64_t* isect_ids,
+                       int* flatten_ids, cudaStream_t st);
+size_t radix_sort_workspace_bytes(int64_t M, int end_bit);
+cudaError_t launch_radix_sort(int64_t M, int end_bit, const int64_t* keys_in, int64_t* keys_out, const int* vals_in,
+                              int* vals_out, void* ws, size_t ws_bytes, cudaStream_t st);
+void launch_offset_encode(int n_isects, const int64_t* isect_ids, int C, int n_tiles, int tile_bits, int* offsets,
+                          cudaStream_t st);
+void launch_tile_hist(int CN, int N, const float* means2d, const int* radii, int tile_size, int tile_w, int tile_h,
+                      int* tiles_per_gauss, int* counts, cudaStream_t st);
+void launch_tile_scan(int n_bins, int* counts, int* offsets, int* cursor, int* n_isects, int cap, int* overflow,
+                      cudaStream_t st);
+void launch_bin_emit_packed(int CN, int N, const float4* rec, const uint2* bbox, int tile_w, int tile_h, int* cursor,
+                            uint64_t* keys, int cap, const int* stop, cudaStream_t st);
+void launch_bin_emit_soa(int CN, int N, const float* means2d, const int* radii, const float* depths, int tile_size,
+                         int tile_w, int tile_h, int* cursor, uint64_t* keys, int cap, cudaStream_t st);
+void launch_tile_sort(int C, int n_tiles, int tile_bits, const int* offsets, uint64_t* keys, int* flatten_ids,
+                      int64_t* isect_ids, int cap, const int* stop, cudaStream_t st);
+
+// ---- raster_fwd.cu / raster_bwd.cu
+void launch_raster_fwd_packed(int C, int W, int H, int tile_w, int tile_h, const float4* rec, const int* tile_offsets,
+                              const int* n_isects_dev, const int* flatten_ids, float* render_depth,
+                              float* render_alphas, int* last_ids, int normalize, const int* stop, cudaStream_t st);
+int launch_raster_fwd_soa(int cdim, int C, int W, int H, int tile_w, int tile_h, const float* means2d,
+                          const float* conics, const float* colors, const float* opacities, const float* backgrounds,
+                          const int* tile_offsets, int n_isects, const int* flatten_ids, float* render_colors,
+                          float* render_alphas, int* last_ids, cudaStream_t st);
+void launch_raster_bwd_lift(int C, int N, int W, int H, int tile_w, int tile_h, const float4* rec,
+                            const int* tile_offsets, const int* n_isects_dev, const int* flatten_ids,
+                            const float* render_alphas, const int* last_ids, const float* v_depth,
+                            const float* v_alpha, const float* means, const float* quats, const float* scales,
+                            const float* viewmats, const float* Ks, float eps2d, float* partials, const int* stop,
+                            cudaStream_t st);
+int launch_raster_bwd_soa(int cdim, int C, int N, int W, int H, int tile_w, int tile_h, const float* means2d,
+                          const float* conics, const float* colors, const float* opacities, const float* backgrounds,
+                          const int* tile_offsets, int n_isects, const int* flatten_ids, const float* render_alphas,
+                          const int* last_ids, const float* v_render_colors, const float* v_render_alphas,
+                          float* v_means2d, float* v_conics, float* v_colors, float* v_opacities, cudaStream_t st);
+
+// ---- loss.cu
+void loss_grid(int W, int H, int* gx, int* gy);
+void launch_loss(int C, int W, int H, const float* ed, const float* alpha, const float* gt, size_t gt_cam_stride,
+                 int apply_mask, float w_d, float w_s, int mode, float* v_out, float* v_alpha, float* partial,
+                 const int* stop, cudaStream_t st);
+
+// ---- pose.cu
+void launch_pose_begin(int C, const gsb_pose_state* state, float* viewmats, cudaStream_t st);
+void launch_pose_finish(int C, int n_tiles, int n_loss_blocks, const float* partials, const float* loss_partials,
+                        const float* viewmats, gsb_pose_state* state, int* stop, gsb_tracker_config cfg,
+                        float inv_pixels, float* history, int history_cap, cudaStream_t st);
+
+// ---- sh.cu
+void launch_sh_fwd(int n, int K, int degree, const float* dirs, const float* coeffs, const uint8_t* masks,
+                   float* colors, cudaStream_t st);
+void launch_sh_bwd(int n, int K, int degree, const float* dirs, const float* coeffs, const uint8_t* masks,
+                   const float* v_colors, float* v_coeffs, float* v_dirs, cudaStream_t st);
+
+}  // namespace gsb

@@ -1,0 +1,333 @@
+// Back-to-front replay of the compositing and its VJP (Appendix A.5 / A.6).
+//
+// One 256-thread block per (camera, 16x16 tile); each warp owns an 8x4 pixel patch.  For every sorted Gaussian the
+// per-pixel gradient terms (v_xy[2], v_conic[3], v_colour[CDIM], v_opacity) are summed over the warp with a
+// halving butterfly (log2 steps, 9 shuffles for 8 values instead of 40).
+//   LIFT = true (tracker): the warp sums land in a per-warp slot of shared memory (no atomics, fixed order =
+//       deterministic); after each batch one thread per Gaussian adds the 8 warp slots and pushes the 6 numbers
+//       straight through the projection Jacobian (A.6) into a 12-float d(loss)/d(viewmat[:3,:4]) accumulator. The
+//       block writes ONE 12-float partial per tile; no per-Gaussian gradient ever reaches HBM.
+//   LIFT = false (op-level twin of gsplat rasterize_to_pixels_bwd): warp sums go to global atomics.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace gsb {
+
+#define BWD_BATCH 128
+
+template <int NV>
+__device__ __forceinline__ void warp_reduce_multi(float (&v)[NV], int lane);
+
+// After the call, lane L holds in v[0] the warp total of value ((L>>4)&1)*4 + ((L>>3)&1)*2 + ((L>>2)&1).
+template <>
+__device__ __forceinline__ void warp_reduce_multi<8>(float (&v)[8], int lane) {
+    bool up = lane & 16;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float keep = up ? v[i + 4] : v[i], send = up ? v[i] : v[i + 4];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+    up = lane & 8;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        float keep = up ? v[i + 2] : v[i], send = up ? v[i] : v[i + 2];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+    up = lane & 4;
+    {
+        float keep = up ? v[1] : v[0], send = up ? v[0] : v[1];
+        v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    }
+    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 2);
+    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+}
+
+// After the call, lane L holds the total of value ((L>>4)&1)*8 + ((L>>3)&1)*4 + ((L>>2)&1)*2 + ((L>>1)&1).
+template <>
+__device__ __forceinline__ void warp_reduce_multi<16>(float (&v)[16], int lane) {
+    bool up = lane & 16;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        float keep = up ? v[i + 8] : v[i], send = up ? v[i] : v[i + 8];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+    up = lane & 8;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float keep = up ? v[i + 4] : v[i], send = up ? v[i] : v[i + 4];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+    up = lane & 4;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        float keep = up ? v[i + 2] : v[i], send = up ? v[i] : v[i + 2];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    }
+    up = lane & 2;
+    {
+        float keep = up ? v[1] : v[0], send = up ? v[0] : v[1];
+        v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+    }
+    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+}
+
+template <int CDIM>
+struct BwdCfg {
+    static constexpr int RS = (CDIM <= 2) ? 8 : ((CDIM <= 6) ? 12 : 16);  // staged floats per Gaussian
+    static constexpr int NV = (6 + CDIM <= 8) ? 8 : 16;                    // reduced values (padded)
+};
+
+template <int CDIM, bool PACKED, bool LIFT>
+__global__ void __launch_bounds__(256) raster_bwd_kernel(
+    int C, int N, int W, int H, int tile_w, int tile_h, const float4* __restrict__ rec,
+    const float* __restrict__ means2d, const float* __restrict__ conics, const float* __restrict__ colors,
+    const float* __restrict__ opacities, const float* __restrict__ backgrounds,
+    const int* __restrict__ tile_offsets, const int* __restrict__ n_isects_dev, int n_isects_host,
+    const int* __restrict__ flatten_ids, const float* __restrict__ render_alphas, const int* __restrict__ last_ids,
+    const float* __restrict__ v_render_colors, const float* __restrict__ v_render_alphas,
+    float* __restrict__ v_means2d, float* __restrict__ v_conics, float* __restrict__ v_colors,
+    float* __restrict__ v_opacities, const float* __restrict__ means, const float* __restrict__ quats,
+    const float* __restrict__ scales, const float* __restrict__ viewmats, const float* __restrict__ Ks, float eps2d,
+    float* __restrict__ partials, const int* __restrict__ stop) {
+    constexpr int RS = BwdCfg<CDIM>::RS;
+    constexpr int NV = BwdCfg<CDIM>::NV;
+    __shared__ __align__(16) float sm[BWD_BATCH * RS];
+    __shared__ int s_id[BWD_BATCH];
+    __shared__ __align__(16) float s_acc[LIFT ? 8 * BWD_BATCH * 6 : 4];
+    __shared__ float s_red[12 * 8];
+    __shared__ int s_max[8];
+
+    const int cam = blockIdx.z;
+    if (stop && stop[cam]) return;
+    const int tile_id = blockIdx.y * tile_w + blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int j = blockIdx.x * 16 + (wid & 1) * 8 + (lane & 7);
+    const int i = blockIdx.y * 16 + (wid >> 1) * 4 + (lane >> 3);
+    const float px = (float)j + 0.5f, py = (float)i + 0.5f;
+    const bool inside = (i < H) && (j < W);
+    const size_t pix = ((size_t)cam * H + min(i, H - 1)) * W + min(j, W - 1);
+    const int n_isects = n_isects_dev ? *n_isects_dev : n_isects_host;
+    const int bin = cam * tile_w * tile_h + tile_id;
+    const int range_start = tile_offsets[bin];
+    const int range_end = (bin == C * tile_w * tile_h - 1) ? n_isects : tile_offsets[bin + 1];
+
+    const float T_final = inside ? 1.f - render_alphas[pix] : 1.f;
+    float T = T_final;
+    float buffer[CDIM], v_rc[CDIM];
+#pragma unroll
+    for (int k = 0; k < CDIM; ++k) {
+        buffer[k] = 0.f;
+        v_rc[k] = inside ? v_render_colors[pix * CDIM + k] : 0.f;
+    }
+    float v_ra = inside ? v_render_alphas[pix] : 0.f;
+    if (backgrounds) {  // colour_out = out + T_final * bg  ->  d/dalpha_out = -bg . v_rc
+#pragma unroll
+        for (int k = 0; k < CDIM; ++k) v_ra -= backgrounds[cam * CDIM + k] * v_rc[k];
+    }
+    const int bin_final = inside ? last_ids[pix] : 0;
+    int warp_bin_final = bin_final;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) warp_bin_final = max(warp_bin_final, __shfl_xor_sync(0xffffffffu, warp_bin_final, o));
+    if (lane == 0) s_max[wid] = warp_bin_final;
+    __syncthreads();
+    int block_bin_final = s_max[0];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) block_bin_final = max(block_bin_final, s_max[w]);
+
+    Cam camera;
+    float pose_acc[12];
+    if (LIFT) {
+        camera = load_cam(viewmats + cam * 16, Ks + cam * 9);
+#pragma unroll
+        for (int k = 0; k < 12; ++k) pose_acc[k] = 0.f;
+    }
+
+    // positions > block_bin_final were composited by no pixel of this tile: start the replay there
+    const int first = min(range_end - 1, block_bin_final);
+    const int num_batches = (first >= range_start) ? (first - range_start + BWD_BATCH) / BWD_BATCH : 0;
+
+    for (int b = 0; b < num_batches; ++b) {
+        __syncthreads();  // previous batch fully consumed
+        const int batch_end = first - BWD_BATCH * b;
+        const int batch_size = min(BWD_BATCH, batch_end + 1 - range_start);
+        if (tid < batch_size) {
+            const int g = flatten_ids[batch_end - tid];
+            s_id[tid] = g;
+            float* dst = sm + tid * RS;
+            if (PACKED) {
+                float4 r0 = rec[2 * (size_t)g], r1 = rec[2 * (size_t)g + 1];
+                reinterpret_cast<float4*>(dst)[0] = make_float4(r0.x, r0.y, r1.x, r1.y);
+                reinterpret_cast<float4*>(dst)[1] = make_float4(r1.z, r0.w, r0.z, 0.f);
+            } else {
+                float2 xy = reinterpret_cast<const float2*>(means2d)[g];
+                reinterpret_cast<float4*>(dst)[0] =
+                    make_float4(xy.x, xy.y, conics[3 * (size_t)g], conics[3 * (size_t)g + 1]);
+                dst[4] = conics[3 * (size_t)g + 2];
+                dst[5] = opacities[g];
+#pragma unroll
+                for (int k = 0; k < CDIM; ++k) dst[6 + k] = colors[(size_t)g * CDIM + k];
+            }
+        }
+        if (LIFT) {
+            float4* z = reinterpret_cast<float4*>(s_acc);
+            for (int q = tid; q < 8 * BWD_BATCH * 6 / 4; q += 256) z[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        __syncthreads();
+
+        for (int t = max(0, batch_end - warp_bin_final); t < batch_size; ++t) {
+            bool valid = inside && (batch_end - t <= bin_final);
+            float alpha = 0.f, opac = 0.f, vis = 0.f, dx = 0.f, dy = 0.f;
+            const float4 p0 = reinterpret_cast<const float4*>(sm + t * RS)[0];
+            const float4 p1 = reinterpret_cast<const float4*>(sm + t * RS)[1];
+            if (valid) {
+                opac = p1.y;
+                dx = p0.x - px; dy = p0.y - py;
+                const float sigma = 0.5f * (p0.z * dx * dx + p1.x * dy * dy) + p0.w * dx * dy;
+                vis = __expf(-sigma);
+                alpha = fminf(GSB_ALPHA_MAX, opac * vis);
+                if (sigma < 0.f || alpha < GSB_ALPHA_MIN) valid = false;
+            }
+            if (!__any_sync(0xffffffffu, valid)) continue;
+            // v[]: 0,1 = v_xy; 2,3,4 = v_conic; 5 = v_opacity (generic) ; 6.. = v_colour
+            //      LIFT: 5 = v_colour (depth) and v_opacity is not needed
+            float v[NV];
+#pragma unroll
+            for (int k = 0; k < NV; ++k) v[k] = 0.f;
+            if (valid) {
+                const float ra = 1.f / (1.f - alpha);
+                T *= ra;
+                const float fac = alpha * T;
+                float col[CDIM];
+                col[0] = p1.z;
+                if (CDIM > 1) col[1 < CDIM ? 1 : 0] = p1.w;
+#pragma unroll
+                for (int k = 2; k < CDIM; ++k) col[k] = sm[t * RS + 6 + k];
+                float v_alpha = 0.f;
+#pragma unroll
+                for (int k = 0; k < CDIM; ++k) {
+                    v[(LIFT ? 5 : 6) + k] = fac * v_rc[k];
+                    v_alpha += (col[k] * T - buffer[k] * ra) * v_rc[k];
+                }
+                v_alpha += T_final * ra * v_ra;
+                if (opac * vis <= GSB_ALPHA_MAX) {
+                    const float v_sigma = -opac * vis * v_alpha;
+                    v[2] = 0.5f * v_sigma * dx * dx;
+                    v[3] = v_sigma * dx * dy;
+                    v[4] = 0.5f * v_sigma * dy * dy;
+                    v[0] = v_sigma * (p0.z * dx + p0.w * dy);
+                    v[1] = v_sigma * (p0.w * dx + p1.x * dy);
+                    if (!LIFT) v[5] = vis * v_alpha;
+                }
+#pragma unroll
+                for (int k = 0; k < CDIM; ++k) buffer[k] += col[k] * fac;
+            }
+            warp_reduce_multi<NV>(v, lane);
+            if (NV == 8) {
+                const int idx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+                if ((lane & 3) == 0) {
+                    if (LIFT) {
+                        if (idx < 6) s_acc[(wid * BWD_BATCH + t) * 6 + idx] = v[0];
+                    } else if (idx < 6 + CDIM) {
+                        const size_t g = (size_t)s_id[t];
+                        float* dst = idx < 2 ? v_means2d + 2 * g + idx
+                                   : idx < 5 ? v_conics + 3 * g + (idx - 2)
+                                   : idx == 5 ? v_opacities + g : v_colors + g * CDIM + (idx - 6);
+                        atomicAdd(dst, v[0]);
+                    }
+                }
+            } else {
+                const int idx = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+                if ((lane & 1) == 0 && idx < 6 + CDIM) {
+                    const size_t g = (size_t)s_id[t];
+                    float* dst = idx < 2 ? v_means2d + 2 * g + idx
+                               : idx < 5 ? v_conics + 3 * g + (idx - 2)
+                               : idx == 5 ? v_opacities + g : v_colors + g * CDIM + (idx - 6);
+                    atomicAdd(dst, v[0]);
+                }
+            }
+        }
+
+        if (LIFT) {
+            __syncthreads();
+            if (tid < batch_size) {
+                float gsum[6];
+#pragma unroll
+                for (int k = 0; k < 6; ++k) gsum[k] = 0.f;
+#pragma unroll
+                for (int w = 0; w < 8; ++w) {
+                    const float2* src = reinterpret_cast<const float2*>(s_acc + (w * BWD_BATCH + tid) * 6);
+                    float2 a = src[0], bq = src[1], cq = src[2];
+                    gsum[0] += a.x; gsum[1] += a.y; gsum[2] += bq.x; gsum[3] += bq.y; gsum[4] += cq.x; gsum[5] += cq.y;
+                }
+                bool any = false;
+#pragma unroll
+                for (int k = 0; k < 6; ++k) any |= (gsum[k] != 0.f);
+                if (any) {
+                    const int n = s_id[tid] - cam * N;
+                    float mean[3] = {means[n * 3], means[n * 3 + 1], means[n * 3 + 2]};
+                    float4 q4 = reinterpret_cast<const float4*>(quats)[n];
+                    float q[4] = {q4.x, q4.y, q4.z, q4.w};
+                    float s[3] = {scales[n * 3], scales[n * 3 + 1], scales[n * 3 + 2]};
+                    Proj p; float S[6], Sc[6];
+                    project_gaussian(camera, mean, q, s, W, H, eps2d, -1e30f, 1e30f, -1.f, p, S, Sc);
+                    float v_pc[3], vS[6];
+                    project_vjp(camera, p, Sc, gsum[0], gsum[1], gsum[2], gsum[3], gsum[4], gsum[5], v_pc, vS);
+                    pose_accumulate(camera, mean, S, v_pc, vS, pose_acc, pose_acc + 9);
+                }
+            }
+        }
+    }
+
+    if (LIFT) {
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 12; ++k) {
+            float s = warp_sum(pose_acc[k]);
+            if (lane == 0) s_red[k * 8 + wid] = s;
+        }
+        __syncthreads();
+        if (tid < 12) {
+            float s = 0.f;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) s += s_red[tid * 8 + w];
+            partials[(size_t)bin * 12 + tid] = s;
+        }
+    }
+}
+
+void launch_raster_bwd_lift(int C, int N, int W, int H, int tile_w, int tile_h, const float4* rec,
+                            const int* tile_offsets, const int* n_isects_dev, const int* flatten_ids,
+                            const float* render_alphas, const int* last_ids, const float* v_depth,
+                            const float* v_alpha, const float* means, const float* quats, const float* scales,
+                            const float* viewmats, const float* Ks, float eps2d, float* partials, const int* stop,
+                            cudaStream_t st) {
+    if (C * tile_w * tile_h == 0) return;
+    dim3 grid(tile_w, tile_h, C);
+    raster_bwd_kernel<1, true, true><<<grid, 256, 0, st>>>(
+        C, N, W, H, tile_w, tile_h, rec, nullptr, nullptr, nullptr, nullptr, nullptr, tile_offsets, n_isects_dev, 0,
+        flatten_ids, render_alphas, last_ids, v_depth, v_alpha, nullptr, nullptr, nullptr, nullptr, means, quats,
+        scales, viewmats, Ks, eps2d, partials, stop);
+}
+
+int launch_raster_bwd_soa(int cdim, int C, int N, int W, int H, int tile_w, int tile_h, const float* means2d,
+                          const float* conics, const float* colors, const float* opacities, const float* backgrounds,
+                          const int* tile_offsets, int n_isects, const int* flatten_ids, const float* render_alphas,
+                          const int* last_ids, const float* v_render_colors, const float* v_render_alphas,
+                          float* v_means2d, float* v_conics, float* v_colors, float* v_opacities, cudaStream_t st) {
+    if (C * tile_w * tile_h == 0) return 0;
+    dim3 grid(tile_w, tile_h, C);
+#define GSB_CASE(D)                                                                                                 \
+    case D:                                                                                                         \
+        raster_bwd_kernel<D, false, false><<<grid, 256, 0, st>>>(                                                   \
+            C, N, W, H, tile_w, tile_h, nullptr, means2d, conics, colors, opacities, backgrounds, tile_offsets,     \
+            nullptr, n_isects, flatten_ids, render_alphas, last_ids, v_render_colors, v_render_alphas, v_means2d,   \
+            v_conics, v_colors, v_opacities, nullptr, nullptr, nullptr, nullptr, nullptr, 0.f, nullptr, nullptr);   \
+        return 0;
+    switch (cdim) {
+        GSB_CASE(1) GSB_CASE(2) GSB_CASE(3) GSB_CASE(4) GSB_CASE(5) GSB_CASE(8)
+        default: return -1;
+    }
+#undef GSB_CASE
+}
+
+}  // namespace gsb

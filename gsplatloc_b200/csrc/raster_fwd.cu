@@ -1,0 +1,149 @@
+// Per-tile front-to-back compositing (Appendix A.4).
+// One 256-thread block per (camera, 16x16 tile); sorted Gaussians are gathered in batches of 256 into shared
+// memory as 32/48-byte records and broadcast-read by all pixels of the tile.
+//   PACKED = true : tracker path. Gaussians come as the two-sector record written by project_bin_kernel and the
+//                   single colour channel is the depth (render_mode "D"/"ED"); the ED quotient can be fused into
+//                   the epilogue.
+//   PACKED = false: op-level twin of gsplat rasterize_to_pixels_fwd (SoA means2d / conics / colors / opacities).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace gsb {
+
+template <int CDIM>
+struct RecStride {
+    static constexpr int value = (CDIM <= 2) ? 8 : ((CDIM <= 6) ? 12 : 16);  // floats per staged record
+};
+
+template <int CDIM, bool PACKED>
+__device__ __forceinline__ void stage_gaussian(float* __restrict__ dst, int g, const float4* __restrict__ rec,
+                                               const float* __restrict__ means2d, const float* __restrict__ conics,
+                                               const float* __restrict__ colors, const float* __restrict__ opac) {
+    // dst: {x, y, a, b | c, opac, col0, col1 | col2 ...}
+    if (PACKED) {
+        float4 r0 = rec[2 * (size_t)g], r1 = rec[2 * (size_t)g + 1];
+        reinterpret_cast<float4*>(dst)[0] = make_float4(r0.x, r0.y, r1.x, r1.y);
+        reinterpret_cast<float4*>(dst)[1] = make_float4(r1.z, r0.w, r0.z, 0.f);
+    } else {
+        float2 xy = reinterpret_cast<const float2*>(means2d)[g];
+        float a = conics[3 * (size_t)g], b = conics[3 * (size_t)g + 1], c = conics[3 * (size_t)g + 2];
+        reinterpret_cast<float4*>(dst)[0] = make_float4(xy.x, xy.y, a, b);
+        dst[4] = c;
+        dst[5] = opac[g];
+#pragma unroll
+        for (int k = 0; k < CDIM; ++k) dst[6 + k] = colors[(size_t)g * CDIM + k];
+    }
+}
+
+template <int CDIM, bool PACKED>
+__global__ void __launch_bounds__(256) raster_fwd_kernel(
+    int C, int W, int H, int tile_w, int tile_h, const float4* __restrict__ rec, const float* __restrict__ means2d,
+    const float* __restrict__ conics, const float* __restrict__ colors, const float* __restrict__ opacities,
+    const float* __restrict__ backgrounds, const int* __restrict__ tile_offsets, const int* __restrict__ n_isects_dev,
+    int n_isects_host, const int* __restrict__ flatten_ids, float* __restrict__ render_colors,
+    float* __restrict__ render_alphas, int* __restrict__ last_ids, int normalize_last, const int* __restrict__ stop) {
+    constexpr int RS = RecStride<CDIM>::value;
+    __shared__ __align__(16) float sm[256 * RS];
+    const int cam = blockIdx.z;
+    if (stop && stop[cam]) return;
+    const int tile_id = blockIdx.y * tile_w + blockIdx.x;
+    const int tid = threadIdx.y * 16 + threadIdx.x;
+    const int i = blockIdx.y * 16 + threadIdx.y, j = blockIdx.x * 16 + threadIdx.x;
+    const float px = (float)j + 0.5f, py = (float)i + 0.5f;
+    const bool inside = (i < H) && (j < W);
+    bool done = !inside;
+    const int n_isects = n_isects_dev ? *n_isects_dev : n_isects_host;
+    const int bin = cam * tile_w * tile_h + tile_id;
+    const int range_start = tile_offsets[bin];
+    const int range_end = (bin == C * tile_w * tile_h - 1) ? n_isects : tile_offsets[bin + 1];
+    const int num_batches = (range_end - range_start + 255) / 256;
+
+    float T = 1.f;
+    int cur_idx = 0;
+    float out[CDIM];
+#pragma unroll
+    for (int k = 0; k < CDIM; ++k) out[k] = 0.f;
+
+    for (int b = 0; b < num_batches; ++b) {
+        if (__syncthreads_count(done) >= 256) break;
+        const int batch_start = range_start + 256 * b;
+        const int idx = batch_start + tid;
+        if (idx < range_end)
+            stage_gaussian<CDIM, PACKED>(sm + tid * RS, flatten_ids[idx], rec, means2d, conics, colors, opacities);
+        __syncthreads();
+        const int batch_size = min(256, range_end - batch_start);
+        for (int t = 0; (t < batch_size) && !done; ++t) {
+            const float4 p0 = reinterpret_cast<const float4*>(sm + t * RS)[0];
+            const float4 p1 = reinterpret_cast<const float4*>(sm + t * RS)[1];
+            const float dx = p0.x - px, dy = p0.y - py;
+            const float sigma = 0.5f * (p0.z * dx * dx + p1.x * dy * dy) + p0.w * dx * dy;
+            const float alpha = fminf(GSB_ALPHA_MAX, p1.y * __expf(-sigma));
+            if (sigma < 0.f || alpha < GSB_ALPHA_MIN) continue;
+            const float next_T = T * (1.f - alpha);
+            if (next_T <= GSB_T_STOP) {  // this entry is NOT composited
+                done = true;
+                break;
+            }
+            const float vis = alpha * T;
+            out[0] += p1.z * vis;
+            if (CDIM > 1) out[1 < CDIM ? 1 : 0] += p1.w * vis;
+#pragma unroll
+            for (int k = 2; k < CDIM; ++k) out[k] += sm[t * RS + 6 + k] * vis;
+            cur_idx = batch_start + t;
+            T = next_T;
+        }
+    }
+    if (inside) {
+        const size_t pix = ((size_t)cam * H + i) * W + j;
+        const float alpha = 1.f - T;
+        render_alphas[pix] = alpha;
+#pragma unroll
+        for (int k = 0; k < CDIM; ++k) {
+            float v = backgrounds ? out[k] + T * backgrounds[cam * CDIM + k] : out[k];
+            if (normalize_last && k == CDIM - 1) v = v / fmaxf(alpha, 1e-10f);  // "ED": A.4 / rendering.py
+            render_colors[pix * CDIM + k] = v;
+        }
+        last_ids[pix] = cur_idx;
+    }
+}
+
+template <int CDIM, bool PACKED>
+static void launch_t(int C, int W, int H, int tile_w, int tile_h, const float4* rec, const float* means2d,
+                     const float* conics, const float* colors, const float* opacities, const float* backgrounds,
+                     const int* tile_offsets, const int* n_isects_dev, int n_isects_host, const int* flatten_ids,
+                     float* render_colors, float* render_alphas, int* last_ids, int normalize_last, const int* stop,
+                     cudaStream_t st) {
+    dim3 grid(tile_w, tile_h, C), block(16, 16, 1);
+    raster_fwd_kernel<CDIM, PACKED><<<grid, block, 0, st>>>(C, W, H, tile_w, tile_h, rec, means2d, conics, colors,
+                                                            opacities, backgrounds, tile_offsets, n_isects_dev,
+                                                            n_isects_host, flatten_ids, render_colors, render_alphas,
+                                                            last_ids, normalize_last, stop);
+}
+
+void launch_raster_fwd_packed(int C, int W, int H, int tile_w, int tile_h, const float4* rec, const int* tile_offsets,
+                              const int* n_isects_dev, const int* flatten_ids, float* render_depth,
+                              float* render_alphas, int* last_ids, int normalize, const int* stop, cudaStream_t st) {
+    if (C * tile_w * tile_h == 0) return;
+    launch_t<1, true>(C, W, H, tile_w, tile_h, rec, nullptr, nullptr, nullptr, nullptr, nullptr, tile_offsets,
+                      n_isects_dev, 0, flatten_ids, render_depth, render_alphas, last_ids, normalize, stop, st);
+}
+
+int launch_raster_fwd_soa(int cdim, int C, int W, int H, int tile_w, int tile_h, const float* means2d,
+                          const float* conics, const float* colors, const float* opacities, const float* backgrounds,
+                          const int* tile_offsets, int n_isects, const int* flatten_ids, float* render_colors,
+                          float* render_alphas, int* last_ids, cudaStream_t st) {
+    if (C * tile_w * tile_h == 0) return 0;
+#define GSB_CASE(D)                                                                                             \
+    case D:                                                                                                     \
+        launch_t<D, false>(C, W, H, tile_w, tile_h, nullptr, means2d, conics, colors, opacities, backgrounds,   \
+                           tile_offsets, nullptr, n_isects, flatten_ids, render_colors, render_alphas, last_ids, \
+                           0, nullptr, st);                                                                     \
+        return 0;
+    switch (cdim) {
+        GSB_CASE(1) GSB_CASE(2) GSB_CASE(3) GSB_CASE(4) GSB_CASE(5) GSB_CASE(8)
+        default: return -1;
+    }
+#undef GSB_CASE
+}
+
+}  // namespace gsb

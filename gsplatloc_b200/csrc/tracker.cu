@@ -1,0 +1,410 @@
+// Device-resident pose-optimisation runtime: owns the buffers of one frame (Gaussians, observation, C pose
+// hypotheses), enqueues the nine kernels of an iteration, replays them as a CUDA graph and polls the early-stop
+// flag.  This is the B200 twin of the inner loop of Runner.train (src/my_gsplat/gs_trainer_total.py:78-267): no
+// autograd graph, no per-step host synchronisation, no allocation inside the loop.
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace gsb {
+extern thread_local std::string g_err;
+int fail(int code, const char* what, cudaError_t e);
+}  // namespace gsb
+using namespace gsb;
+
+#define TCK(call, what)                                              \
+    do {                                                             \
+        cudaError_t e_ = (call);                                     \
+        if (e_ != cudaSuccess) return fail(GSB_ERR_CUDA, what, e_);  \
+    } while (0)
+
+struct gsb_tracker {
+    int C = 0, W = 0, H = 0, tile_w = 0, tile_h = 0, n_tiles = 0, tile_bits = 0;
+    int N = 0, N_cap = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    gsb_tracker_config cfg;
+    float *means = nullptr, *quats = nullptr, *scales = nullptr, *opac = nullptr;
+    float *gt = nullptr, *Ks = nullptr, *viewmats = nullptr;
+    gsb_pose_state* state = nullptr;
+    int* stop = nullptr;
+    float4* rec = nullptr;
+    uint2* bbox = nullptr;
+    int *counts = nullptr, *offsets = nullptr, *cursor = nullptr, *n_isects = nullptr, *overflow = nullptr;
+    uint64_t* keys = nullptr;
+    int* flatten_ids = nullptr;
+    int64_t cap = 0;
+    float *ed = nullptr, *alpha = nullptr, *v_depth = nullptr, *v_alpha = nullptr;
+    int* last_ids = nullptr;
+    float *partials = nullptr, *loss_partials = nullptr;
+    int n_loss_blocks = 0;
+    float* history = nullptr;
+    int history_cap = 0;
+    int* h_flags = nullptr;  // pinned: [C] stop flags, then n_isects, overflow
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    bool graph_valid = false, have_map = false, have_obs = false, have_pose = false, cap_dirty = true;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int64_t total_launches = 0;
+    int64_t last_n_isects = 0;
+};
+
+static const int kLaunchesPerIter = 9;
+
+static void invalidate_graph(gsb_tracker* t) {
+    if (t->exec) cudaGraphExecDestroy(t->exec);
+    if (t->graph) cudaGraphDestroy(t->graph);
+    t->exec = nullptr; t->graph = nullptr; t->graph_valid = false;
+}
+
+static void enqueue_iteration(gsb_tracker* t, bool forward_only) {
+    cudaStream_t st = t->stream;
+    const gsb_tracker_config& c = t->cfg;
+    const int C = t->C, N = t->N;
+    launch_pose_begin(C, t->state, t->viewmats, st);
+    launch_project_bin(C, N, t->means, t->quats, t->scales, t->opac, t->viewmats, t->Ks, t->W, t->H, t->tile_w,
+                       t->tile_h, c.eps2d, c.near_plane, c.far_plane, c.radius_clip, t->rec, t->bbox, t->counts,
+                       t->stop, st);
+    launch_tile_scan(C * t->n_tiles, t->counts, t->offsets, t->cursor, t->n_isects, (int)t->cap, t->overflow, st);
+    launch_bin_emit_packed(C * N, N, t->rec, t->bbox, t->tile_w, t->tile_h, t->cursor, t->keys, (int)t->cap, t->stop, st);
+    launch_tile_sort(C, t->n_tiles, t->tile_bits, t->offsets, t->keys, t->flatten_ids, nullptr, (int)t->cap, t->stop, st);
+    launch_raster_fwd_packed(C, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->offsets, t->n_isects, t->flatten_ids,
+                             t->ed, t->alpha, t->last_ids, 1, t->stop, st);
+    if (forward_only) return;
+    const float inv_p = 1.f / ((float)t->W * (float)t->H);
+    launch_loss(C, t->W, t->H, t->ed, t->alpha, t->gt, 0, 1, c.depth_lambda * inv_p,
+                (1.f - c.depth_lambda - c.normal_lambda) * inv_p, 1, t->v_depth, t->v_alpha, t->loss_partials,
+                t->stop, st);
+    launch_raster_bwd_lift(C, N, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->offsets, t->n_isects, t->flatten_ids,
+                           t->alpha, t->last_ids, t->v_depth, t->v_alpha, t->means, t->quats, t->scales, t->viewmats,
+                           t->Ks, c.eps2d, t->partials, t->stop, st);
+    launch_pose_finish(C, t->n_tiles, t->n_loss_blocks, t->partials, t->loss_partials, t->viewmats, t->state, t->stop,
+                       c, inv_p, t->history, t->history_cap, st);
+}
+
+// Size the intersection buffers from a counting pass at the current poses (one sync, outside the loop).
+static int ensure_capacity(gsb_tracker* t) {
+    cudaStream_t st = t->stream;
+    const gsb_tracker_config& c = t->cfg;
+    launch_pose_begin(t->C, t->state, t->viewmats, st);
+    launch_project_bin(t->C, t->N, t->means, t->quats, t->scales, t->opac, t->viewmats, t->Ks, t->W, t->H, t->tile_w,
+                       t->tile_h, c.eps2d, c.near_plane, c.far_plane, c.radius_clip, t->rec, t->bbox, t->counts,
+                       t->stop, st);
+    launch_tile_scan(t->C * t->n_tiles, t->counts, t->offsets, t->cursor, t->n_isects, 0x7fffffff, nullptr, st);
+    TCK(cudaMemcpyAsync(t->h_flags + t->C, t->n_isects, sizeof(int), cudaMemcpyDeviceToHost, st), "n_isects d2h");
+    TCK(cudaStreamSynchronize(st), "capacity pass");
+    t->total_launches += 3;
+    int64_t m = t->h_flags[t->C];
+    if (m > t->cap || t->cap == 0) {
+        int64_t want = m + m / 4 + 65536;
+        if (t->keys) cudaFree(t->keys);
+        if (t->flatten_ids) cudaFree(t->flatten_ids);
+        t->keys = nullptr; t->flatten_ids = nullptr;
+        TCK(cudaMalloc(&t->keys, sizeof(uint64_t) * (size_t)want), "alloc keys");
+        TCK(cudaMalloc(&t->flatten_ids, sizeof(int) * (size_t)want), "alloc flatten_ids");
+        t->cap = want;
+        invalidate_graph(t);
+    }
+    t->cap_dirty = false;
+    return GSB_OK;
+}
+
+static void rotmat_to_quat_kornia(const float* M /*4x4 row-major*/, float* q) {
+    // kornia.geometry.rotation_matrix_to_quaternion (wxyz, eps 1e-8), model.py:32 via transform.py:69-84
+    double m00 = M[0], m01 = M[1], m02 = M[2], m10 = M[4], m11 = M[5], m12 = M[6], m20 = M[8], m21 = M[9], m22 = M[10];
+    double tr = m00 + m11 + m22, eps = 1e-8, w, x, y, z;
+    if (tr > 0) {
+        double s = sqrt(tr + 1.0 + eps) * 2;
+        w = 0.25 * s; x = (m21 - m12) / s; y = (m02 - m20) / s; z = (m10 - m01) / s;
+    } else if (m00 > m11 && m00 > m22) {
+        double s = sqrt(1.0 + m00 - m11 - m22 + eps) * 2;
+        w = (m21 - m12) / s; x = 0.25 * s; y = (m01 + m10) / s; z = (m02 + m20) / s;
+    } else if (m11 > m22) {
+        double s = sqrt(1.0 + m11 - m00 - m22 + eps) * 2;
+        w = (m02 - m20) / s; x = (m01 + m10) / s; y = 0.25 * s; z = (m12 + m21) / s;
+    } else {
+        double s = sqrt(1.0 + m22 - m00 - m11 + eps) * 2;
+        w = (m10 - m01) / s; x = (m02 + m20) / s; y = (m12 + m21) / s; z = 0.25 * s;
+    }
+    q[0] = (float)w; q[1] = (float)x; q[2] = (float)y; q[3] = (float)z;
+}
+
+extern "C" {
+
+void gsb_tracker_default_config(gsb_tracker_config* cfg, int max_steps) {
+    cfg->lr_quat = 5e-4f; cfg->lr_trans = 1e-3f;
+    cfg->wd_quat = 1e-3f; cfg->wd_trans = 1e-3f;
+    cfg->beta1 = 0.9f; cfg->beta2 = 0.999f; cfg->adam_eps = 1e-8f;
+    cfg->lr_gamma = (float)pow(0.2, 1.0 / (double)(max_steps > 0 ? max_steps : 1000));
+    cfg->depth_lambda = 0.8f; cfg->normal_lambda = 0.f;
+    cfg->early_stop = 1; cfg->patience = 200; cfg->warmup = 100;
+    cfg->eps2d = 0.3f; cfg->near_plane = 1e-2f; cfg->far_plane = 1e10f; cfg->radius_clip = 0.f;
+}
+
+int gsb_tracker_create(gsb_tracker** out, int C, int W, int H, void* stream) {
+    if (!out || C <= 0 || W <= 0 || H <= 0) return fail(GSB_ERR_ARG, "gsb_tracker_create: bad sizes", cudaSuccess);
+    int dev_count = 0;
+    TCK(cudaGetDeviceCount(&dev_count), "gsb_tracker_create: no CUDA device");
+    gsb_tracker* t = new gsb_tracker();
+    t->C = C; t->W = W; t->H = H;
+    t->tile_w = (W + GSB_TILE - 1) / GSB_TILE; t->tile_h = (H + GSB_TILE - 1) / GSB_TILE;
+    t->n_tiles = t->tile_w * t->tile_h;
+    t->tile_bits = (int)floor(log2((double)t->n_tiles)) + 1;
+    gsb_tracker_default_config(&t->cfg, 1000);
+    if (stream) t->stream = (cudaStream_t)stream;
+    else { TCK(cudaStreamCreateWithFlags(&t->stream, cudaStreamNonBlocking), "stream"); t->own_stream = true; }
+    const size_t P = (size_t)C * W * H, nb = (size_t)C * t->n_tiles;
+    int gx, gy;
+    loss_grid(W, H, &gx, &gy);
+    t->n_loss_blocks = gx * gy;
+    t->history_cap = 4096;
+    TCK(cudaMalloc(&t->gt, sizeof(float) * (size_t)W * H), "alloc");
+    TCK(cudaMalloc(&t->Ks, sizeof(float) * 9 * C), "alloc");
+    TCK(cudaMalloc(&t->viewmats, sizeof(float) * 16 * C), "alloc");
+    TCK(cudaMalloc(&t->state, sizeof(gsb_pose_state) * C), "alloc");
+    TCK(cudaMalloc(&t->stop, sizeof(int) * C), "alloc");
+    TCK(cudaMalloc(&t->counts, sizeof(int) * nb), "alloc");
+    TCK(cudaMalloc(&t->offsets, sizeof(int) * (nb + 1)), "alloc");
+    TCK(cudaMalloc(&t->cursor, sizeof(int) * nb), "alloc");
+    TCK(cudaMalloc(&t->n_isects, sizeof(int) * 2), "alloc");
+    t->overflow = t->n_isects + 1;
+    TCK(cudaMalloc(&t->ed, sizeof(float) * P), "alloc");
+    TCK(cudaMalloc(&t->alpha, sizeof(float) * P), "alloc");
+    TCK(cudaMalloc(&t->v_depth, sizeof(float) * P), "alloc");
+    TCK(cudaMalloc(&t->v_alpha, sizeof(float) * P), "alloc");
+    TCK(cudaMalloc(&t->last_ids, sizeof(int) * P), "alloc");
+    TCK(cudaMalloc(&t->partials, sizeof(float) * nb * 12), "alloc");
+    TCK(cudaMalloc(&t->loss_partials, sizeof(float) * (size_t)C * t->n_loss_blocks * 2), "alloc");
+    TCK(cudaMalloc(&t->history, sizeof(float) * (size_t)t->history_cap * C * 8), "alloc");
+    TCK(cudaMallocHost(&t->h_flags, sizeof(int) * (C + 2)), "alloc pinned");
+    TCK(cudaMemsetAsync(t->counts, 0, sizeof(int) * nb, t->stream), "memset");
+    TCK(cudaMemsetAsync(t->stop, 0, sizeof(int) * C, t->stream), "memset");
+    TCK(cudaMemsetAsync(t->n_isects, 0, sizeof(int) * 2, t->stream), "memset");
+    TCK(cudaMemsetAsync(t->partials, 0, sizeof(float) * nb * 12, t->stream), "memset");
+    TCK(cudaEventCreate(&t->ev0), "event");
+    TCK(cudaEventCreate(&t->ev1), "event");
+    *out = t;
+    return GSB_OK;
+}
+
+void gsb_tracker_destroy(gsb_tracker* t) {
+    if (!t) return;
+    cudaStreamSynchronize(t->stream);
+    invalidate_graph(t);
+    void* bufs[] = {t->means, t->quats, t->scales, t->opac, t->gt, t->Ks, t->viewmats, t->state, t->stop, t->rec,
+                    t->bbox, t->counts, t->offsets, t->cursor, t->n_isects, t->keys, t->flatten_ids, t->ed, t->alpha,
+                    t->v_depth, t->v_alpha, t->last_ids, t->partials, t->loss_partials, t->history};
+    for (void* b : bufs)
+        if (b) cudaFree(b);
+    if (t->h_flags) cudaFreeHost(t->h_flags);
+    if (t->ev0) cudaEventDestroy(t->ev0);
+    if (t->ev1) cudaEventDestroy(t->ev1);
+    if (t->own_stream) cudaStreamDestroy(t->stream);
+    delete t;
+}
+
+int gsb_tracker_set_config(gsb_tracker* t, const gsb_tracker_config* cfg) {
+    if (!t || !cfg) return fail(GSB_ERR_ARG, "gsb_tracker_set_config: null", cudaSuccess);
+    t->cfg = *cfg;
+    invalidate_graph(t);  // the config is baked into kernel arguments
+    t->cap_dirty = true;
+    return GSB_OK;
+}
+
+int gsb_tracker_set_map(gsb_tracker* t, int N, const float* means, const float* quats, const float* scales,
+                        const float* opacities, int on_host) {
+    if (!t || N <= 0) return fail(GSB_ERR_ARG, "gsb_tracker_set_map: bad arguments", cudaSuccess);
+    if (N > t->N_cap) {
+        TCK(cudaStreamSynchronize(t->stream), "sync");
+        void* old[] = {t->means, t->quats, t->scales, t->opac, t->rec, t->bbox};
+        for (void* b : old)
+            if (b) cudaFree(b);
+        size_t n = (size_t)N;
+        TCK(cudaMalloc(&t->means, sizeof(float) * 3 * n), "alloc map");
+        TCK(cudaMalloc(&t->quats, sizeof(float) * 4 * n), "alloc map");
+        TCK(cudaMalloc(&t->scales, sizeof(float) * 3 * n), "alloc map");
+        TCK(cudaMalloc(&t->opac, sizeof(float) * n), "alloc map");
+        TCK(cudaMalloc(&t->rec, sizeof(float4) * 2 * n * t->C), "alloc rec");
+        TCK(cudaMalloc(&t->bbox, sizeof(uint2) * n * t->C), "alloc bbox");
+        t->N_cap = N;
+        invalidate_graph(t);
+    }
+    if (N != t->N) invalidate_graph(t);  // grid sizes are baked into the graph
+    t->N = N;
+    cudaMemcpyKind k = on_host ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
+    TCK(cudaMemcpyAsync(t->means, means, sizeof(float) * 3 * (size_t)N, k, t->stream), "copy means");
+    TCK(cudaMemcpyAsync(t->quats, quats, sizeof(float) * 4 * (size_t)N, k, t->stream), "copy quats");
+    TCK(cudaMemcpyAsync(t->scales, scales, sizeof(float) * 3 * (size_t)N, k, t->stream), "copy scales");
+    TCK(cudaMemcpyAsync(t->opac, opacities, sizeof(float) * (size_t)N, k, t->stream), "copy opacities");
+    t->have_map = true; t->cap_dirty = true;
+    return GSB_OK;
+}
+
+int gsb_tracker_set_observation(gsb_tracker* t, const float* depth, int on_host, const float* K_host) {
+    if (!t || !depth || !K_host) return fail(GSB_ERR_ARG, "gsb_tracker_set_observation: null", cudaSuccess);
+    TCK(cudaMemcpyAsync(t->gt, depth, sizeof(float) * (size_t)t->W * t->H,
+                        on_host ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, t->stream), "copy depth");
+    std::vector<float> ks((size_t)t->C * 9);
+    for (int c = 0; c < t->C; ++c) memcpy(ks.data() + c * 9, K_host, sizeof(float) * 9);
+    TCK(cudaMemcpyAsync(t->Ks, ks.data(), sizeof(float) * ks.size(), cudaMemcpyHostToDevice, t->stream), "copy K");
+    TCK(cudaStreamSynchronize(t->stream), "sync");  // ks is a temporary
+    t->have_obs = true;
+    return GSB_OK;
+}
+
+int gsb_tracker_set_poses(gsb_tracker* t, const float* c2w_init_host, const float* c2w_gt_host) {
+    if (!t || !c2w_init_host) return fail(GSB_ERR_ARG, "gsb_tracker_set_poses: null", cudaSuccess);
+    std::vector<gsb_pose_state> st((size_t)t->C);
+    for (int c = 0; c < t->C; ++c) {
+        gsb_pose_state& s = st[c];
+        memset(&s, 0, sizeof s);
+        const float* M = c2w_init_host + c * 16;
+        rotmat_to_quat_kornia(M, s.q);
+        s.t[0] = M[3]; s.t[1] = M[7]; s.t[2] = M[11];
+        s.lr_q = t->cfg.lr_quat; s.lr_t = t->cfg.lr_trans;
+        s.best_loss = s.best_depth_loss = s.best_edge_loss = s.best_eT = s.best_eR = INFINITY;
+        s.best_iter = -1;
+        if (c2w_gt_host) {
+            s.has_gt = 1;
+            memcpy(s.gt_c2w, c2w_gt_host + c * 16, sizeof(float) * 12);
+        }
+    }
+    TCK(cudaMemcpyAsync(t->state, st.data(), sizeof(gsb_pose_state) * st.size(), cudaMemcpyHostToDevice, t->stream), "copy state");
+    TCK(cudaMemsetAsync(t->stop, 0, sizeof(int) * t->C, t->stream), "memset stop");
+    TCK(cudaMemsetAsync(t->overflow, 0, sizeof(int), t->stream), "memset overflow");
+    TCK(cudaStreamSynchronize(t->stream), "sync");
+    t->have_pose = true; t->cap_dirty = true;
+    return GSB_OK;
+}
+
+static int capture_graph(gsb_tracker* t) {
+    invalidate_graph(t);
+    TCK(cudaStreamBeginCapture(t->stream, cudaStreamCaptureModeThreadLocal), "begin capture");
+    enqueue_iteration(t, false);
+    cudaError_t e = cudaStreamEndCapture(t->stream, &t->graph);
+    if (e != cudaSuccess) return fail(GSB_ERR_CUDA, "end capture", e);
+    TCK(cudaGraphInstantiate(&t->exec, t->graph, 0), "graph instantiate");
+    t->graph_valid = true;
+    return GSB_OK;
+}
+
+int gsb_tracker_run(gsb_tracker* t, int n_iters, int poll_every, int use_graph, int* iters_done, float* elapsed_ms) {
+    if (!t || !t->have_map || !t->have_obs || !t->have_pose)
+        return fail(GSB_ERR_ARG, "gsb_tracker_run: map, observation and poses must be set first", cudaSuccess);
+    if (t->cap_dirty) {
+        int rc = ensure_capacity(t);
+        if (rc) return rc;
+    }
+    if (use_graph && !t->graph_valid) {
+        int rc = capture_graph(t);
+        if (rc) return rc;
+    }
+    TCK(cudaEventRecord(t->ev0, t->stream), "event");
+    int done = 0;
+    bool all_stopped = false;
+    for (int it = 0; it < n_iters && !all_stopped; ++it) {
+        if (use_graph) TCK(cudaGraphLaunch(t->exec, t->stream), "graph launch");
+        else enqueue_iteration(t, false);
+        ++done;
+        if (poll_every > 0 && (it + 1) % poll_every == 0 && it + 1 < n_iters) {
+            TCK(cudaMemcpyAsync(t->h_flags, t->stop, sizeof(int) * t->C, cudaMemcpyDeviceToHost, t->stream), "poll");
+            TCK(cudaStreamSynchronize(t->stream), "poll sync");
+            all_stopped = true;
+            for (int c = 0; c < t->C; ++c) all_stopped &= (t->h_flags[c] != 0);
+        }
+    }
+    TCK(cudaEventRecord(t->ev1, t->stream), "event");
+    TCK(cudaMemcpyAsync(t->h_flags + t->C, t->n_isects, sizeof(int) * 2, cudaMemcpyDeviceToHost, t->stream), "flags");
+    TCK(cudaStreamSynchronize(t->stream), "run sync");
+    TCK(cudaGetLastError(), "run");
+    t->total_launches += (int64_t)done * kLaunchesPerIter;
+    t->last_n_isects = t->h_flags[t->C];
+    if (iters_done) *iters_done = done;
+    if (elapsed_ms) TCK(cudaEventElapsedTime(elapsed_ms, t->ev0, t->ev1), "elapsed");
+    if (t->h_flags[t->C + 1]) {
+        t->cap_dirty = true;  // regrow on the next run
+        t->cap = 0;
+        cudaMemsetAsync(t->overflow, 0, sizeof(int), t->stream);
+        return fail(GSB_ERR_OVERFLOW, "gsb_tracker_run: intersection buffer overflowed; poses must be reset and the run repeated", cudaSuccess);
+    }
+    return GSB_OK;
+}
+
+int gsb_tracker_forward(gsb_tracker* t) {
+    if (!t || !t->have_map || !t->have_pose)
+        return fail(GSB_ERR_ARG, "gsb_tracker_forward: map and poses must be set first", cudaSuccess);
+    if (!t->have_obs) return fail(GSB_ERR_ARG, "gsb_tracker_forward: intrinsics (set_observation) must be set first", cudaSuccess);
+    if (t->cap_dirty) {
+        int rc = ensure_capacity(t);
+        if (rc) return rc;
+    }
+    enqueue_iteration(t, true);
+    TCK(cudaMemcpyAsync(t->h_flags + t->C, t->n_isects, sizeof(int) * 2, cudaMemcpyDeviceToHost, t->stream), "flags");
+    TCK(cudaStreamSynchronize(t->stream), "forward sync");
+    TCK(cudaGetLastError(), "forward");
+    t->total_launches += 6;
+    t->last_n_isects = t->h_flags[t->C];
+    return GSB_OK;
+}
+
+int gsb_tracker_get_states(gsb_tracker* t, gsb_pose_state* out_host) {
+    if (!t || !out_host) return fail(GSB_ERR_ARG, "gsb_tracker_get_states: null", cudaSuccess);
+    TCK(cudaMemcpyAsync(out_host, t->state, sizeof(gsb_pose_state) * t->C, cudaMemcpyDeviceToHost, t->stream), "states");
+    TCK(cudaStreamSynchronize(t->stream), "states sync");
+    return GSB_OK;
+}
+
+int gsb_tracker_get_render(gsb_tracker* t, float* depth, float* alpha, int on_host) {
+    if (!t) return fail(GSB_ERR_ARG, "gsb_tracker_get_render: null", cudaSuccess);
+    const size_t bytes = sizeof(float) * (size_t)t->C * t->W * t->H;
+    cudaMemcpyKind k = on_host ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
+    if (depth) TCK(cudaMemcpyAsync(depth, t->ed, bytes, k, t->stream), "render depth");
+    if (alpha) TCK(cudaMemcpyAsync(alpha, t->alpha, bytes, k, t->stream), "render alpha");
+    TCK(cudaStreamSynchronize(t->stream), "render sync");
+    return GSB_OK;
+}
+
+int gsb_tracker_get_history(gsb_tracker* t, int camera, float* out_host, int max_rows) {
+    if (!t || camera < 0 || camera >= t->C || !out_host) { fail(GSB_ERR_ARG, "gsb_tracker_get_history: bad arguments", cudaSuccess); return -1; }
+    gsb_pose_state s;
+    if (cudaMemcpy(&s, t->state + camera, sizeof s, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    int rows = std::min(std::min(s.iter + (s.stopped ? 1 : 0), t->history_cap), max_rows);
+    if (rows <= 0) return 0;
+    if (cudaMemcpy2D(out_host, sizeof(float) * 8, t->history + (size_t)camera * 8, sizeof(float) * 8 * t->C,
+                     sizeof(float) * 8, rows, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    return rows;
+}
+
+int gsb_tracker_get_counters(gsb_tracker* t, int64_t* n_isects, int64_t* capacity, int* launches_per_iter,
+                             int64_t* total_launches) {
+    if (!t) return fail(GSB_ERR_ARG, "gsb_tracker_get_counters: null", cudaSuccess);
+    if (n_isects) *n_isects = t->last_n_isects;
+    if (capacity) *capacity = t->cap;
+    if (launches_per_iter) *launches_per_iter = kLaunchesPerIter;
+    if (total_launches) *total_launches = t->total_launches;
+    return GSB_OK;
+}
+
+void* gsb_tracker_stream(gsb_tracker* t) { return t ? (void*)t->stream : nullptr; }
+
+int gsb_tracker_debug_copy(gsb_tracker* t, int32_t* flatten_ids, int32_t* offsets, float* records) {
+    if (!t) return fail(GSB_ERR_ARG, "gsb_tracker_debug_copy: null", cudaSuccess);
+    cudaStream_t st = t->stream;
+    if (flatten_ids && t->last_n_isects > 0)
+        TCK(cudaMemcpyAsync(flatten_ids, t->flatten_ids, sizeof(int) * (size_t)t->last_n_isects, cudaMemcpyDeviceToDevice, st), "debug copy");
+    if (offsets)
+        TCK(cudaMemcpyAsync(offsets, t->offsets, sizeof(int) * ((size_t)t->C * t->n_tiles + 1), cudaMemcpyDeviceToDevice, st), "debug copy");
+    if (records)
+        TCK(cudaMemcpyAsync(records, t->rec, sizeof(float) * 8 * (size_t)t->C * t->N, cudaMemcpyDeviceToDevice, st), "debug copy");
+    TCK(cudaStreamSynchronize(st), "debug copy sync");
+    return GSB_OK;
+}
+
+}  // extern "C"

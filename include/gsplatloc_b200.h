@@ -1,0 +1,171 @@
+/* gsplatloc_b200 — C ABI of the B200-native depth-splat pose-optimisation hot path.
+ *
+ * Drop-in boundary for the path GsplatLoc drives through gsplat:
+ *   Python boundary  : gsplat.rasterization(...)            src/my_gsplat/model.py:195-213, geometry.py:117-132
+ *   op-level boundary: gsplat.cuda._wrapper -> _C ops       .vscode/PythonImportHelper-v2-Completion.json
+ *                      (fully_fused_projection IDX:14351, isect_tiles IDX:14360, isect_offset_encode IDX:14369,
+ *                       rasterize_to_pixels IDX:14378, spherical_harmonics IDX:14306)
+ *   loop boundary    : Runner.train() inner loop            src/my_gsplat/gs_trainer_total.py:78-267
+ *
+ * Conventions: every pointer is a DEVICE pointer unless the name ends in _host; all tensors are dense, row-major,
+ * fp32 / int32 / int64 as stated; `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ * Every call returns 0 on success or a non-zero code; gsb_last_error() gives the message (thread-local).
+ * Nothing here allocates on behalf of the caller except the tracker object, which owns its buffers.
+ * There is no CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef GSPLATLOC_B200_H
+#define GSPLATLOC_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSB_OK 0
+#define GSB_ERR_CUDA 1
+#define GSB_ERR_ARG 2
+#define GSB_ERR_OVERFLOW 3 /* tile-intersection buffer too small; call again (the tracker regrows itself) */
+
+const char* gsb_last_error(void);
+int gsb_version(void);
+
+/* ---- gsplat fully_fused_projection (IDX:14351; fwd kernel IDX:14270).  means[N,3] quats[N,4] scales[N,3]
+ * viewmats[C,4,4] Ks[C,3,3] -> radii[C,N] i32, means2d[C,N,2], depths[C,N], conics[C,N,3] (zero when culled). */
+int gsb_projection_fwd(int C, int N, const float* means, const float* quats, const float* scales,
+                       const float* viewmats, const float* Ks, int width, int height, float eps2d, float near_plane,
+                       float far_plane, float radius_clip, int32_t* radii, float* means2d, float* depths,
+                       float* conics, void* stream);
+
+/* ---- gsplat _FullyFusedProjection.backward (IDX:14270).  Any of v_means[N,3] v_quats[N,4] v_scales[N,3]
+ * v_viewmats[C,4,4] may be NULL (not computed); non-NULL outputs are ACCUMULATED into (zero them first). */
+int gsb_projection_bwd(int C, int N, const float* means, const float* quats, const float* scales,
+                       const float* viewmats, const float* Ks, int width, int height, float eps2d,
+                       const int32_t* radii, const float* v_means2d, const float* v_depths, const float* v_conics,
+                       float* v_means, float* v_quats, float* v_scales, float* v_viewmats, void* stream);
+
+/* ---- gsplat isect_tiles (IDX:14360).  Two calls because the number of intersections is data dependent
+ * (the reference syncs on cumsum[-1] the same way):
+ *   gsb_isect_count : tiles_per_gauss[C,N] i32 and per-(camera,tile) offsets[C*T+1] i32; returns M in *n_isects_host
+ *                     (synchronises `stream`).  counts_ws: 2*C*T+4 ints of scratch.
+ *   gsb_isect_emit  : isect_ids[M] i64 (cam|tile|depth bits, sorted when sort!=0), flatten_ids[M] i32.
+ * method 0 = "tile" route (per-tile bins sorted in shared memory), 1 = "radix" route (global stable radix sort,
+ * the reference's shape).  Both give bit-identical outputs when sort != 0; sort == 0 requires method 1. */
+int gsb_isect_count(int C, int N, const float* means2d, const int32_t* radii, int tile_size, int tile_width,
+                    int tile_height, int32_t* tiles_per_gauss, int32_t* offsets, int32_t* counts_ws,
+                    int64_t* n_isects_host, void* stream);
+size_t gsb_isect_emit_workspace(int C, int N, int64_t n_isects, int tile_width, int tile_height, int method);
+int gsb_isect_emit(int C, int N, const float* means2d, const int32_t* radii, const float* depths,
+                   const int32_t* tiles_per_gauss, const int32_t* offsets, int tile_size, int tile_width,
+                   int tile_height, int sort, int method, int64_t n_isects, int64_t* isect_ids, int32_t* flatten_ids,
+                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- gsplat isect_offset_encode (IDX:14369): sorted isect_ids[M] -> offsets[C,tile_h,tile_w] i32. */
+int gsb_isect_offset_encode(int64_t n_isects, const int64_t* isect_ids, int C, int tile_width, int tile_height,
+                            int32_t* offsets, void* stream);
+
+/* ---- gsplat rasterize_to_pixels (IDX:14378; fwd IDX:14279).  tile_size must be 16 (the reference's default).
+ * means2d[C,N,2] conics[C,N,3] colors[C,N,D] opacities[C,N] backgrounds[C,D]|NULL offsets[C,th,tw] flatten_ids[M]
+ * -> render_colors[C,H,W,D], render_alphas[C,H,W,1], last_ids[C,H,W] i32.  D in {1,2,3,4,5,8}. */
+int gsb_rasterize_fwd(int C, int N, int D, const float* means2d, const float* conics, const float* colors,
+                      const float* opacities, const float* backgrounds, int width, int height, int tile_size,
+                      const int32_t* offsets, const int32_t* flatten_ids, int64_t n_isects, float* render_colors,
+                      float* render_alphas, int32_t* last_ids, void* stream);
+/* outputs v_means2d[C,N,2] v_conics[C,N,3] v_colors[C,N,D] v_opacities[C,N] are ACCUMULATED into. */
+int gsb_rasterize_bwd(int C, int N, int D, const float* means2d, const float* conics, const float* colors,
+                      const float* opacities, const float* backgrounds, int width, int height, int tile_size,
+                      const int32_t* offsets, const int32_t* flatten_ids, int64_t n_isects,
+                      const float* render_alphas, const int32_t* last_ids, const float* v_render_colors,
+                      const float* v_render_alphas, float* v_means2d, float* v_conics, float* v_colors,
+                      float* v_opacities, void* stream);
+
+/* ---- gsplat spherical_harmonics (IDX:14306), degrees 0 and 1 (GsplatLoc uses sh_degree=1, model.py:128).
+ * dirs[n,3] coeffs[n,K,3] masks[n] u8|NULL -> colors[n,3].  bwd accumulates v_coeffs[n,K,3], v_dirs[n,3]|NULL. */
+int gsb_sh_fwd(int n, int K, int degree, const float* dirs, const float* coeffs, const uint8_t* masks, float* colors,
+               void* stream);
+int gsb_sh_bwd(int n, int K, int degree, const float* dirs, const float* coeffs, const uint8_t* masks,
+               const float* v_colors, float* v_coeffs, float* v_dirs, void* stream);
+
+/* ---- fused losses: compute_depth_loss + compute_silhouette_loss (src/my_gsplat/loss.py:10-59) with the trainer's
+ * mask (gs_trainer_total.py:109,126-137).  depth[C,H,W], gt[H,W] (gt_per_camera=0) or [C,H,W].
+ * apply_mask: B = gt * (depth != 0) as the trainer does; 0: inputs are already masked.
+ * -> sums_host-free: loss_sums[C,2] = {sum|A-B|, sum|E(A)-E(B)|} (divide by H*W for the means) and
+ * v_depth[C,H,W] = w_d * dLd/ddepth + w_s * dLs/ddepth with w_* INCLUDING the 1/(H*W).
+ * partial_ws: 2*C*ceil(W/32)*ceil(H/8) floats. */
+int gsb_depth_edge_loss(int C, int width, int height, const float* depth, const float* gt, int gt_per_camera,
+                        int apply_mask, float w_d, float w_s, float* loss_sums, float* v_depth, float* partial_ws,
+                        void* stream);
+
+/* ================= device-resident pose optimisation loop (Runner.train inner loop) ================= */
+
+typedef struct gsb_tracker_config {
+    float lr_quat, lr_trans;       /* CameraConfig, model.py:18-23: 5e-4, 1e-3 */
+    float wd_quat, wd_trans;       /* coupled L2 weight decay 1e-3 */
+    float beta1, beta2, adam_eps;  /* torch Adam defaults .9 .999 1e-8 */
+    float lr_gamma;                /* ExponentialLR gamma = 0.2**(1/max_steps), gs_trainer_total.py:65-72 */
+    float depth_lambda;            /* 0.8, base.py:27 */
+    float normal_lambda;           /* 0.0, base.py:28 */
+    int early_stop;                /* base.py:34 */
+    int patience;                  /* 200, base.py:35 */
+    int warmup;                    /* best-loss tracking starts when step > 100, gs_trainer_total.py:171 */
+    float eps2d, near_plane, far_plane, radius_clip; /* 0.3, 1e-2, 1e10, 0 (model.py:119-133, A.1) */
+} gsb_tracker_config;
+
+/* One per camera / pose hypothesis.  Mirrors CameraOptModule_quat_tans + its two Adam states + the early-stop
+ * fields the reference keeps in Config (base.py:34-43). */
+typedef struct gsb_pose_state {
+    float q[4], t[3];              /* quat_cur (wxyz), t_cur: camera-to-world */
+    float m_q[4], v_q[4], m_t[3], v_t[3];
+    float lr_q, lr_t;
+    int adam_step;
+    int iter;                      /* loop index ("step" in the reference) of the NEXT iteration */
+    int counter, stopped;
+    float best_loss, best_depth_loss, best_edge_loss, best_eT, best_eR;
+    int best_iter;
+    float best_q[4], best_t[3];
+    float loss, depth_loss, edge_loss, normal_loss, eT, eR; /* last evaluated iteration */
+    float g_q[4], g_t[3];          /* last d(loss)/d(quat_cur), d(loss)/d(t_cur) */
+    float g_viewmat[12];           /* last d(loss)/d(viewmat[:3,:4]) row-major */
+    int has_gt;
+    float gt_c2w[12];              /* ground-truth pose rows 0..2 (for eT/eR, eval/utils.py:122-168) */
+} gsb_pose_state;
+
+typedef struct gsb_tracker gsb_tracker;
+
+void gsb_tracker_default_config(gsb_tracker_config* cfg, int max_steps);
+/* stream: cudaStream_t the tracker launches on (NULL: it creates its own non-blocking stream). */
+int gsb_tracker_create(gsb_tracker** out, int n_cameras, int width, int height, void* stream);
+void gsb_tracker_destroy(gsb_tracker* t);
+int gsb_tracker_set_config(gsb_tracker* t, const gsb_tracker_config* cfg);
+/* Gaussians (GSModel, model.py:136-175): means[N,3] quats[N,4] scales[N,3] opacities[N] (post-sigmoid).
+ * on_host != 0: pointers are host memory and are copied asynchronously (pin them for full speed). */
+int gsb_tracker_set_map(gsb_tracker* t, int N, const float* means, const float* quats, const float* scales,
+                        const float* opacities, int on_host);
+/* observed depth image [H,W] (train_data.src_depth) and intrinsics K[3,3] (host) */
+int gsb_tracker_set_observation(gsb_tracker* t, const float* depth, int on_host, const float* K_host);
+/* initial camera-to-world poses [C,4,4] (host), optional ground truth [C,4,4] (host) for eT/eR; resets Adam,
+ * learning rates and early-stop state (a fresh CameraOptModule_quat_tans, gs_trainer_total.py:63-72). */
+int gsb_tracker_set_poses(gsb_tracker* t, const float* c2w_init_host, const float* c2w_gt_host);
+/* Run up to n_iters iterations (all cameras in lock-step; a camera whose early stop fired is frozen).
+ * poll_every: how often the host looks at the stop flags (0: only at the end).  use_graph: replay a CUDA graph
+ * of one iteration.  *iters_done: iterations launched; *elapsed_ms (nullable): device time by CUDA events. */
+int gsb_tracker_run(gsb_tracker* t, int n_iters, int poll_every, int use_graph, int* iters_done, float* elapsed_ms);
+int gsb_tracker_get_states(gsb_tracker* t, gsb_pose_state* out_host);
+/* last forward: depth[C,H,W] (expected depth "ED"), alpha[C,H,W]; either may be NULL; on_host selects D2H */
+int gsb_tracker_get_render(gsb_tracker* t, float* depth, float* alpha, int on_host);
+/* per-iteration history rows {loss, L_d, L_s, L_n, eT, eR, |g_q|, |g_t|} of camera c; returns rows written */
+int gsb_tracker_get_history(gsb_tracker* t, int camera, float* out_host, int max_rows);
+/* sizes of the last iteration: n_isects (M), isect capacity, launches per iteration */
+int gsb_tracker_get_counters(gsb_tracker* t, int64_t* n_isects, int64_t* capacity, int* launches_per_iter,
+                             int64_t* total_launches);
+void* gsb_tracker_stream(gsb_tracker* t);
+/* copies of the tracker's intermediates for parity tests, into caller-allocated DEVICE buffers (any may be NULL):
+ * sorted flatten_ids [M], tile offsets [C*T+1], projected records [C*N,8] = {x,y,depth,opacity,a,b,c,radius bits} */
+int gsb_tracker_debug_copy(gsb_tracker* t, int32_t* flatten_ids, int32_t* offsets, float* records);
+/* one forward only (render at the current poses; used for the GT re-render of geometry.py:69-135) */
+int gsb_tracker_forward(gsb_tracker* t);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
