@@ -384,12 +384,12 @@ def pose_opt_loop(quat0, t0, means, quats, scales, opac, gt, K, W, H, c2w_gt=Non
         eT = eR = float("nan")
         if c2w_gt is not None:
             eT, eR = pose_errors(pose_to_c2w(q.detach(), t.detach()).numpy(), c2w_gt)
-        hist.append((float(tot), float(Ld), float(Ls), eT, eR))
+        hist.append((float(tot.detach()), float(Ld.detach()), float(Ls.detach()), eT, eR))
         if log:
             log(step, hist[-1], q.grad.clone(), t.grad.clone())
         if early_stop and step > warm:
-            if float(tot) < best["loss"]:
-                best.update(loss=float(tot), eT=eT, eR=eR, step=step)
+            if float(tot.detach()) < best["loss"]:
+                best.update(loss=float(tot.detach()), eT=eT, eR=eR, step=step)
                 counter = 0
             else:
                 counter += 1

@@ -6,7 +6,7 @@ import numpy as np
 import torch
 
 from oracle import gsplat_oracle as orc
-from tests import _util as U
+import gsb_testutil as U
 
 
 def _setup(dtype=torch.float64):
@@ -75,7 +75,7 @@ def test_forward_invariants():
 
 def test_stable_ties_keep_emission_order():
     # two Gaussians with bit-identical depth in the same tile: the lower flat index must come first
-    m2 = np.array([[[20.0, 20.0], [24.0, 22.0], [21.0, 19.0]]], dtype=np.float32)
+    m2 = np.array([[[20.0, 20.0], [10.0, 10.0], [21.0, 19.0]]], dtype=np.float32)
     radii = np.array([[6, 6, 6]], dtype=np.int32)
     depths = np.array([[2.0, 1.0, 2.0]], dtype=np.float32)
     tpg, ids, fl = orc.isect_tiles(m2, radii, depths, 16, 4, 4)
@@ -106,5 +106,6 @@ def test_pose_loop_converges_to_the_known_delta():
     res = orc.pose_opt_loop(q0, t0, means, quats, scales, opac, gt, K, fp.W, fp.H, c2w_gt=fp.src_c2w, max_steps=1000,
                             n_steps=60, early_stop=False)
     eT, eR = res["history"][-1][3], res["history"][-1][4]
-    assert res["history"][-1][0] < 0.5 * res["history"][0][0], "loss must drop"
-    assert eT < 0.6 * eT0 and eR < 0.8 * eR0, (eT0, eT, eR0, eR)
+    # the loss floor is set by the coarse splats of a 160x96 frame, so ask for a clear drop, not for zero
+    assert res["history"][-1][0] < 0.9 * res["history"][0][0], "loss must drop"
+    assert eT < 0.4 * eT0 and eR < 0.4 * eR0, (eT0, eT, eR0, eR)
