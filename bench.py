@@ -1,0 +1,379 @@
+#!/usr/bin/env python
+"""Benchmark of the GsplatLoc pose-optimisation hot path (BASELINE.json metric: pose-opt iterations/s at
+1200x680 / ~200k Gaussians, plus achieved HBM GB/s of the dominant kernel).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's sm_100a path
+    python bench.py --impl reference --gpus N --steps K ...  # the CPU restatement of the reference path (oracle/)
+
+A STEP is one frame's pose optimisation: ``--iters`` (default 100, BASELINE.json configs[1]) iterations of
+pose -> projection -> tile intersection + sort -> depth raster -> depth+edge loss -> raster backward lifted to the
+6-DoF pose -> Adam.  ``value`` = iterations/s with the frame resident in HBM; ``e2e`` = the same through the public
+``PoseTracker`` API with HOST (pinned) inputs, the H2D copies of the map and the observation and the D2H read of
+the pose state inside the timed region.  Frames are sharded over ranks (one process per GPU); the only collective
+is the final gather of per-frame pose errors.  One JSON line is printed by rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import numpy as np
+import torch
+
+METRIC = "pose-opt iters/sec (raster fwd+bwd+loss) at 1200x680/200k Gaussians; HBM GB/s"
+UNIT = "iters/s"
+WORKLOADS = {
+    # name: (camera dict name, lattice stride, translation cm, rotation deg)
+    "replica200k": ("REPLICA", 2, 2.0, 1.0),      # BASELINE.json configs[1]  (S2)
+    "replica50k": ("REPLICA", 4, 2.0, 1.0),       # configs[0]               (S1)
+    "tum77k": ("TUM", 2, 6.0, 3.0),               # configs[2]               (S3)
+    "hd500k": ("HD", 2, 2.0, 1.0),                # towards configs[4]       (S5)
+}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0: float, t1: float) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, smax, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ts, line in self.rows:
+            if ts < t0 - 0.05 or ts > t1 + 0.05:
+                continue
+            f = [x.strip() for x in line.split(",")]
+            try:
+                sm.append(float(f[0])); smax = float(f[1])
+            except Exception:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:  # timed region shorter than the sampling period: take whatever we have
+            for ts, line in self.rows[-3:]:
+                f = [x.strip() for x in line.split(",")]
+                try:
+                    sm.append(float(f[0])); smax = float(f[1])
+                except Exception:
+                    pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def make_frames(workload: str, n: int, seed0: int):
+    from gsplatloc_b200 import synthetic as syn
+    cam_name, stride, tcm, rdeg = WORKLOADS[workload]
+    cam = getattr(syn, cam_name)
+    return [syn.make_frame_pair(cam, stride=stride, seed=seed0 + i, trans_cm=tcm, rot_deg=rdeg) for i in range(n)]
+
+
+def algorithmic_bytes(stage: str, C: int, N: int, M: int, P: int, T: int) -> float:
+    """SURVEY.md §8(d) per-unit figures (fp32, ED-only, pose-gradient-only) x the units one launch processes."""
+    return {
+        "project_bin": C * N * (40 + 28) + C * N * (12 + 4),       # proj_fwd + the count half of isect
+        "tile_scan": 12.0 * T,
+        "bin_emit": C * N * (16 + 8) + 12.0 * M,                   # emit reads + key/value write
+        "tile_sort": 8.0 * M + 12.0 * M,                           # one read of the keys, one write of ids (+offsets)
+        "raster_fwd": 32.0 * M + 12.0 * P,
+        "loss": 20.0 * P,
+        "raster_bwd": 32.0 * M + 16.0 * P + 24.0 * C * N,
+        "pose_finish": 48.0 * T,
+        "pose_begin": 64.0 * C,
+    }[stage]
+
+
+def rendered_observation(trk_cls, fp, device, stream=None):
+    """Observation as the reference builds it with normalize=True: a splat render of the source frame's own points
+    from its own pose (src/data/dataset.py:362-372, geometry.py:69-135).  Setup, not timed."""
+    Ns = fp.src_points.shape[0]
+    g = trk_cls(fp.W, fp.H, 1, device=device, stream=stream)
+    g.set_map(torch.tensor(fp.src_points, device=device), torch.tensor([[1.0, 0, 0, 0]], device=device).repeat(Ns, 1),
+              torch.tensor(fp.src_scales, device=device), torch.ones(Ns, device=device))
+    g.set_observation(torch.zeros(fp.H, fp.W, device=device), fp.K)
+    g.set_poses(fp.src_c2w)
+    g.forward()
+    d, _ = g.render()
+    g.close()
+    return d[0].contiguous()
+
+
+def run_native(args, rank, world, local_rank):
+    import torch.distributed as dist
+    from gsplatloc_b200 import PoseTracker, TrackerConfig, _lib
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: gsplatloc_b200 has no CPU path")
+    _lib.lib()  # fail loudly if the extension is not built
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    K, W_, iters = args.steps, args.warmup, args.iters
+    n_pool = args.pool
+    frames = make_frames(args.workload, n_pool, seed0=42 + 1000 * rank)     # rank r owns its own frames
+    cfg = TrackerConfig(max_steps=args.max_steps, early_stop=False)          # fixed 100 steps for timing (S2)
+    host = []
+    trackers = []
+    stream = torch.cuda.Stream(dev)          # every tracker launches here; the timing events are recorded here
+    for fp in frames:
+        N = fp.tar_points.shape[0]
+        obs = rendered_observation(PoseTracker, fp, dev, stream)
+        pin = dict(means=torch.tensor(fp.tar_points).pin_memory(),
+                   quats=torch.tensor([[1.0, 0, 0, 0]]).repeat(N, 1).pin_memory(),
+                   scales=torch.tensor(fp.scales).pin_memory(), opac=torch.ones(N).pin_memory(),
+                   depth=obs.cpu().pin_memory())
+        host.append(pin)
+        t = PoseTracker(fp.W, fp.H, 1, cfg, device=dev, stream=stream)
+        t.set_map(pin["means"].to(dev), pin["quats"].to(dev), pin["scales"].to(dev), pin["opac"].to(dev))
+        t.set_observation(obs, fp.K)
+        t.set_poses(fp.tar_c2w, fp.src_c2w)
+        trackers.append(t)
+    fp0 = frames[0]
+    N, P = fp0.tar_points.shape[0], fp0.W * fp0.H
+    T = ((fp0.W + 15) // 16) * ((fp0.H + 15) // 16)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def step_resident(s):
+        t, fp = trackers[s % n_pool], frames[s % n_pool]
+        t.set_poses(fp.tar_c2w, fp.src_c2w)
+        t.run(iters, poll_every=0, use_graph=True)
+        return t
+
+    def step_e2e(s):
+        t, fp, pin = trackers[s % n_pool], frames[s % n_pool], host[s % n_pool]
+        t.set_map(pin["means"], pin["quats"], pin["scales"], pin["opac"])        # H2D from pinned memory
+        t.set_observation(pin["depth"], fp.K)                                    # H2D
+        t.set_poses(fp.tar_c2w, fp.src_c2w)
+        t.run(iters, poll_every=0, use_graph=True)
+        return t.states()[0]                                                     # D2H
+
+    # ---------------------------------------------------------------- device-resident leg (value)
+    for s in range(W_):
+        step_resident(s)
+    launches0 = sum(t.counters()["total_launches"] for t in trackers)
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    wall0 = time.time()
+    e0.record(stream)
+    for s in range(K):
+        step_resident(W_ + s)
+    e1.record(stream)
+    barrier()
+    wall1 = time.time()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop(wall0, wall1) if sampler else None
+    launches = sum(t.counters()["total_launches"] for t in trackers) - launches0
+    records = []
+    for i, (t, fp) in enumerate(zip(trackers, frames)):
+        st = t.states()[0]
+        records.append([rank, i, st["eT"], st["eR"], st["loss"], *st["q"], *st["t"]])
+    M = int(np.mean([t.counters()["n_isects"] for t in trackers]))
+
+    # ---------------------------------------------------------------- end-to-end leg (host buffers)
+    for s in range(min(W_, 2)):
+        step_e2e(s)
+    barrier()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record(stream)
+    for s in range(K):
+        step_e2e(W_ + s)
+    e3.record(stream)
+    barrier()
+    ms_e2e = e2.elapsed_time(e3)
+    h2d = int(sum(v.numel() * 4 for v in host[0].values())) + 16 * 4 * 2 + 9 * 4
+    d2h = int(__import__("ctypes").sizeof(_lib.PoseState))
+
+    # ---------------------------------------------------------------- per-kernel times (roofline), rank 0 only
+    stage_ms = None
+    if rank == 0:
+        t = trackers[0]
+        t.set_poses(frames[0].tar_c2w, frames[0].src_c2w)
+        t.profile(3)
+        stage_ms = t.profile(20)
+
+    # ---------------------------------------------------------------- max over ranks + the one collective
+    if world > 1:
+        tt = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms, ms_e2e = float(tt[0]), float(tt[1])
+        rec = torch.tensor(records, device=dev, dtype=torch.float32)
+        gathered = [torch.empty_like(rec) for _ in range(world)]
+        dist.all_gather(gathered, rec)                                           # final gather of pose errors (NCCL)
+        records = torch.cat(gathered).cpu().tolist()
+        lt = torch.tensor([launches], device=dev, dtype=torch.float64)
+        dist.all_reduce(lt)
+        launches = int(lt[0])
+    if rank != 0:
+        return
+    total_iters = K * iters * world
+    value = total_iters / (ms * 1e-3)
+    e2e_v = total_iters / (ms_e2e * 1e-3)
+    peak, peak_src = peaks()
+    dom = max((k for k in stage_ms if k not in ("pose_begin", "pose_finish", "tile_scan")), key=lambda k: stage_ms[k])
+    ab = algorithmic_bytes(dom, 1, N, M, P, T)
+    ach = ab / (stage_ms[dom] * 1e-3) / 1e9
+    sum_ms = sum(stage_ms.values())
+    stages = {k: {"ms": round(v, 5), "share": round(v / sum_ms, 4),
+                  "alg_GBps": round(algorithmic_bytes(k, 1, N, M, P, T) / (v * 1e-3) / 1e9, 1) if v > 0 else None}
+              for k, v in stage_ms.items()}
+    iter_bytes = sum(algorithmic_bytes(k, 1, N, M, P, T) for k in stage_ms)
+    eT = np.array([r[2] for r in records]); eR = np.array([r[3] for r in records])
+    out = {
+        "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W_,
+        "ms_per_step": round(ms / K, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: {fp0.W}x{fp0.H}, N={N} Gaussians, M={M} tile intersections, "
+                               f"{iters}-iteration pose optimisation per step (BASELINE.json configs[1])",
+                   "iters_per_step": iters, "gaussians": N, "isects": M, "pixels": P, "tiles": T,
+                   "frames_per_rank": n_pool, "sharding": "independent frames per rank, final all_gather of pose errors",
+                   "l2": f"inputs larger than L2: {n_pool} frames x ~{round((44*N + 24*P + 12*M + 40*N) / 1e6)} MB of "
+                         "buffers cycled between steps; iterations inside a step reuse L2 as the real loop does",
+                   "timing": "CUDA events on the launching stream, barrier+synchronize both sides, max over ranks"},
+        "e2e": {"value": round(e2e_v, 2), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": round(ms_e2e / K, 4)},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
+                     "frac": round(ach / peak, 4), "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": int(ab), "kernel_ms": round(stage_ms[dom], 5),
+                     "iteration": {"algorithmic_bytes": int(iter_bytes), "sum_kernel_ms": round(sum_ms, 5),
+                                   "achieved_GBps": round(iter_bytes / (sum_ms * 1e-3) / 1e9, 1),
+                                   "frac": round(iter_bytes / (sum_ms * 1e-3) / 1e9 / peak, 4)},
+                     "stages": stages},
+        "pose_errors": {"frames": len(records), "ATE_rmse_m": float(np.sqrt((eT ** 2).mean())),
+                        "AAE_rmse_deg": float(np.sqrt((eR ** 2).mean()))},
+    }
+    traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(traffic_file):
+        try:
+            out["roofline"]["traffic"] = json.load(open(traffic_file)).get(args.workload, {}).get(dom)
+        except Exception:
+            pass
+    if not args.no_cpu_baseline and world == 1:
+        out["cpu_baseline"] = cpu_oracle(args.workload, frames[0], n_timed=args.cpu_iters, warm=1)
+    print(json.dumps(out), flush=True)
+
+
+def cpu_oracle(workload, fp, n_timed=2, warm=1):
+    """The CPU restatement (oracle/, kind 'port': the reference's gsplat/kornia code is absent) on the
+    same frame, fp32, all host threads; a bounded sample of ``n_timed`` full iterations (fwd + loss + bwd + Adam)."""
+    from oracle import gsplat_oracle as orc
+    import gsb_testutil as U
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    dt = torch.float32
+    means, quats, scales, opac = U.map_tensors(fp, dt)
+    times = []
+    q0 = torch.tensor(orc.rotmat_to_quat(fp.tar_c2w[:3, :3]), dtype=dt)
+    t0 = torch.tensor(fp.tar_c2w[:3, 3], dtype=dt)
+
+    def log(step, row, gq, gt_):
+        times.append(time.time())
+    t_start = time.time()
+    orc.pose_opt_loop(q0, t0, means, quats, scales, opac, torch.tensor(fp.src_depth), torch.tensor(fp.K), fp.W, fp.H,
+                      c2w_gt=fp.src_c2w, max_steps=1000, n_steps=warm + n_timed + 1, early_stop=False, log=log)
+    # times[i] is stamped after the backward of iteration i; the optimiser step belongs to the next interval
+    dts = np.diff(np.array(times))[warm:]
+    sec = float(np.mean(dts)) if len(dts) else float(time.time() - t_start)
+    return {"value": round(1.0 / sec, 5), "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{len(dts)} full iterations of {workload} ({means.shape[0]} Gaussians, {fp.W}x{fp.H}) after "
+                      f"{warm} warm-up, torch CPU fp32", "s_per_iter": round(sec, 3)}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's own implementation cannot be imported or compiled here (gsplat / kornia
+    absent), so the arm times the oracle port on the host cores; rank 0 only."""
+    if rank != 0:
+        return
+    frames = make_frames(args.workload, 1, seed0=42)
+    steps = max(1, min(args.steps, args.ref_max_steps))
+    warm = max(1, min(args.warmup, 1))
+    t0 = time.time()
+    cb = cpu_oracle(args.workload, frames[0], n_timed=steps, warm=warm)
+    fp = frames[0]
+    out = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": world, "steps": steps,
+           "warmup": warm, "ms_per_step": round(1e3 / cb["value"], 2), "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": f"{args.workload}: {fp.W}x{fp.H}, N={fp.tar_points.shape[0]} Gaussians; each step = ONE "
+                                  "full pose iteration (bounded sample of the 100-iteration optimisation)",
+                      "iters_per_step": 1},
+           "cpu_baseline": cb,
+           "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0, "wall_s": round(time.time() - t0, 1)}
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--workload", default="replica200k", choices=sorted(WORKLOADS))
+    ap.add_argument("--iters", type=int, default=100, help="pose iterations per step (frame)")
+    ap.add_argument("--max-steps", type=int, default=2000, help="LR schedule horizon (GsplatLoc_eval.py --num-iters)")
+    ap.add_argument("--pool", type=int, default=4, help="distinct frames cycled per rank")
+    ap.add_argument("--cpu-iters", type=int, default=2)
+    ap.add_argument("--ref-max-steps", type=int, default=6)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        run_native(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

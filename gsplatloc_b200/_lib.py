@@ -65,6 +65,7 @@ _SIGS = {
     "gsb_tracker_set_poses": (c_i, [c_p, c_p, c_p]),
     "gsb_tracker_run": (c_i, [c_p, c_i, c_i, c_i, C.POINTER(c_i), C.POINTER(c_f)]),
     "gsb_tracker_forward": (c_i, [c_p]),
+    "gsb_tracker_profile": (c_i, [c_p, c_i, c_p]),
     "gsb_tracker_get_states": (c_i, [c_p, c_p]),
     "gsb_tracker_get_render": (c_i, [c_p, c_p, c_p, c_i]),
     "gsb_tracker_get_history": (c_i, [c_p, c_i, c_p, c_i]),

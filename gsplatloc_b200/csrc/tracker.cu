@@ -64,29 +64,43 @@ static void invalidate_graph(gsb_tracker* t) {
     t->exec = nullptr; t->graph = nullptr; t->graph_valid = false;
 }
 
-static void enqueue_iteration(gsb_tracker* t, bool forward_only) {
+// ``marks`` (nullable): kLaunchesPerIter + 1 events recorded around the kernels (profiling mode).
+static void enqueue_iteration(gsb_tracker* t, bool forward_only, cudaEvent_t* marks = nullptr) {
     cudaStream_t st = t->stream;
     const gsb_tracker_config& c = t->cfg;
     const int C = t->C, N = t->N;
+    int mk = 0;
+#define GSB_MARK() do { if (marks) cudaEventRecord(marks[mk++], st); } while (0)
+    GSB_MARK();
     launch_pose_begin(C, t->state, t->viewmats, st);
+    GSB_MARK();
     launch_project_bin(C, N, t->means, t->quats, t->scales, t->opac, t->viewmats, t->Ks, t->W, t->H, t->tile_w,
                        t->tile_h, c.eps2d, c.near_plane, c.far_plane, c.radius_clip, t->rec, t->bbox, t->counts,
                        t->stop, st);
+    GSB_MARK();
     launch_tile_scan(C * t->n_tiles, t->counts, t->offsets, t->cursor, t->n_isects, (int)t->cap, t->overflow, st);
+    GSB_MARK();
     launch_bin_emit_packed(C * N, N, t->rec, t->bbox, t->tile_w, t->tile_h, t->cursor, t->keys, (int)t->cap, t->stop, st);
+    GSB_MARK();
     launch_tile_sort(C, t->n_tiles, t->tile_bits, t->offsets, t->keys, t->flatten_ids, nullptr, (int)t->cap, t->stop, st);
+    GSB_MARK();
     launch_raster_fwd_packed(C, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->offsets, t->n_isects, t->flatten_ids,
                              t->ed, t->alpha, t->last_ids, 1, t->stop, st);
+    GSB_MARK();
     if (forward_only) return;
     const float inv_p = 1.f / ((float)t->W * (float)t->H);
     launch_loss(C, t->W, t->H, t->ed, t->alpha, t->gt, 0, 1, c.depth_lambda * inv_p,
                 (1.f - c.depth_lambda - c.normal_lambda) * inv_p, 1, t->v_depth, t->v_alpha, t->loss_partials,
                 t->stop, st);
+    GSB_MARK();
     launch_raster_bwd_lift(C, N, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->offsets, t->n_isects, t->flatten_ids,
                            t->alpha, t->last_ids, t->v_depth, t->v_alpha, t->means, t->quats, t->scales, t->viewmats,
                            t->Ks, c.eps2d, t->partials, t->stop, st);
+    GSB_MARK();
     launch_pose_finish(C, t->n_tiles, t->n_loss_blocks, t->partials, t->loss_partials, t->viewmats, t->state, t->stop,
                        c, inv_p, t->history, t->history_cap, st);
+    GSB_MARK();
+#undef GSB_MARK
 }
 
 // Size the intersection buffers from a counting pass at the current poses (one sync, outside the loop).
@@ -334,6 +348,34 @@ int gsb_tracker_run(gsb_tracker* t, int n_iters, int poll_every, int use_graph, 
         cudaMemsetAsync(t->overflow, 0, sizeof(int), t->stream);
         return fail(GSB_ERR_OVERFLOW, "gsb_tracker_run: intersection buffer overflowed; poses must be reset and the run repeated", cudaSuccess);
     }
+    return GSB_OK;
+}
+
+int gsb_tracker_profile(gsb_tracker* t, int n_iters, float* stage_ms_host) {
+    if (!t || !t->have_map || !t->have_obs || !t->have_pose || !stage_ms_host || n_iters <= 0)
+        return fail(GSB_ERR_ARG, "gsb_tracker_profile: map, observation and poses must be set first", cudaSuccess);
+    if (t->cap_dirty) {
+        int rc = ensure_capacity(t);
+        if (rc) return rc;
+    }
+    cudaEvent_t marks[kLaunchesPerIter + 1];
+    for (auto& m : marks) TCK(cudaEventCreate(&m), "event");
+    for (int k = 0; k < kLaunchesPerIter; ++k) stage_ms_host[k] = 0.f;
+    for (int it = 0; it < n_iters; ++it) {
+        enqueue_iteration(t, false, marks);
+        TCK(cudaStreamSynchronize(t->stream), "profile sync");
+        for (int k = 0; k < kLaunchesPerIter; ++k) {
+            float ms = 0.f;
+            TCK(cudaEventElapsedTime(&ms, marks[k], marks[k + 1]), "elapsed");
+            stage_ms_host[k] += ms;
+        }
+    }
+    for (int k = 0; k < kLaunchesPerIter; ++k) stage_ms_host[k] /= (float)n_iters;
+    for (auto& m : marks) cudaEventDestroy(m);
+    t->total_launches += (int64_t)n_iters * kLaunchesPerIter;
+    TCK(cudaMemcpyAsync(t->h_flags + t->C, t->n_isects, sizeof(int) * 2, cudaMemcpyDeviceToHost, t->stream), "flags");
+    TCK(cudaStreamSynchronize(t->stream), "profile sync");
+    t->last_n_isects = t->h_flags[t->C];
     return GSB_OK;
 }
 

@@ -67,20 +67,33 @@ def quat_t_to_c2w(q: np.ndarray, t: np.ndarray) -> np.ndarray:
 
 class PoseTracker:
     def __init__(self, width: int, height: int, n_cameras: int = 1, config: Optional[TrackerConfig] = None,
-                 device: str | torch.device = "cuda:0"):
+                 device: str | torch.device = "cuda:0", stream: Optional["torch.cuda.Stream"] = None):
         if not torch.cuda.is_available():
             raise RuntimeError("PoseTracker needs a CUDA device (gsplatloc_b200 has no CPU path)")
         self.device = torch.device(device)
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
         self.W, self.H, self.C = int(width), int(height), int(n_cameras)
         self.config = config or TrackerConfig()
         self._L = _lib.lib()
         self._h = ctypes.c_void_p()
         with torch.cuda.device(self.device):
-            self._stream = torch.cuda.current_stream().cuda_stream
-            _lib.check(self._L.gsb_tracker_create(ctypes.byref(self._h), self.C, self.W, self.H, self._stream),
-                       "tracker_create")
+            # every kernel of the tracker runs on ONE stream: the caller's, or torch's current stream when that is
+            # not the legacy default stream (graphs cannot be captured there), or a new one.  Record CUDA events on
+            # ``tracker.stream`` to time it.
+            if stream is None:
+                cur = torch.cuda.current_stream(self.device)
+                stream = cur if cur.cuda_stream != 0 else torch.cuda.Stream(self.device)
+            self.stream = stream
+            _lib.check(self._L.gsb_tracker_create(ctypes.byref(self._h), self.C, self.W, self.H,
+                                                  self.stream.cuda_stream), "tracker_create")
         self._keep = {}
         self.set_config(self.config)
+
+    def _order_after_producer(self, *tensors):
+        """CUDA inputs were produced on torch's current stream: make the tracker's stream wait for it."""
+        if any(isinstance(t, torch.Tensor) and t.is_cuda for t in tensors):
+            self.stream.wait_stream(torch.cuda.current_stream(self.device))
 
     def close(self):
         if getattr(self, "_h", None) is not None and self._h:
@@ -116,6 +129,7 @@ class PoseTracker:
         on_host = not means.is_cuda
         assert all(t.is_cuda != on_host for t in (quats, scales, opacities)), "map tensors must share a device"
         self._keep["map"] = (means, quats, scales, opacities)
+        self._order_after_producer(means, quats, scales, opacities)
         _lib.check(self._L.gsb_tracker_set_map(self._h, N, means.data_ptr(), quats.data_ptr(), scales.data_ptr(),
                                                opacities.data_ptr(), int(on_host)), "tracker_set_map")
         self.N = N
@@ -124,6 +138,7 @@ class PoseTracker:
         depth = self._f32(depth, (self.H, self.W))
         K = np.ascontiguousarray(np.asarray(torch.as_tensor(K).detach().cpu(), dtype=np.float32).reshape(3, 3))
         self._keep["obs"] = (depth, K)
+        self._order_after_producer(depth)
         _lib.check(self._L.gsb_tracker_set_observation(self._h, depth.data_ptr(), int(not depth.is_cuda),
                                                        K.ctypes.data), "tracker_set_observation")
 
@@ -148,6 +163,16 @@ class PoseTracker:
     def forward(self):
         _lib.check(self._L.gsb_tracker_forward(self._h), "tracker_forward")
 
+    STAGES = ("pose_begin", "project_bin", "tile_scan", "bin_emit", "tile_sort", "raster_fwd", "loss", "raster_bwd",
+              "pose_finish")
+
+    def profile(self, n_iters: int = 10) -> dict:
+        """Mean device time (ms) of every kernel of an iteration, CUDA events on the tracker's stream."""
+        buf = (ctypes.c_float * len(self.STAGES))()
+        _lib.check(self._L.gsb_tracker_profile(self._h, int(n_iters), ctypes.cast(buf, ctypes.c_void_p)),
+                   "tracker_profile")
+        return dict(zip(self.STAGES, [float(x) for x in buf]))
+
     # ------------------------------------------------------------------ outputs
     def states(self) -> list:
         arr = (_lib.PoseState * self.C)()
@@ -160,6 +185,7 @@ class PoseTracker:
     def render(self):
         d = torch.empty((self.C, self.H, self.W), dtype=torch.float32, device=self.device)
         a = torch.empty_like(d)
+        self._order_after_producer(d)
         _lib.check(self._L.gsb_tracker_get_render(self._h, d.data_ptr(), a.data_ptr(), 0), "tracker_get_render")
         return d, a
 
@@ -185,6 +211,7 @@ class PoseTracker:
         fl = torch.empty(M, dtype=torch.int32, device=self.device)
         off = torch.empty(self.C * tw * th + 1, dtype=torch.int32, device=self.device)
         rec = torch.empty((self.C * self.N, 8), dtype=torch.float32, device=self.device)
+        self._order_after_producer(rec)
         _lib.check(self._L.gsb_tracker_debug_copy(self._h, fl.data_ptr(), off.data_ptr(), rec.data_ptr()),
                    "tracker_debug_copy")
         return fl, off, rec

@@ -162,6 +162,10 @@ void* gsb_tracker_stream(gsb_tracker* t);
 /* copies of the tracker's intermediates for parity tests, into caller-allocated DEVICE buffers (any may be NULL):
  * sorted flatten_ids [M], tile offsets [C*T+1], projected records [C*N,8] = {x,y,depth,opacity,a,b,c,radius bits} */
 int gsb_tracker_debug_copy(gsb_tracker* t, int32_t* flatten_ids, int32_t* offsets, float* records);
+/* measurement aid: run n_iters iterations un-graphed with CUDA events between the kernels; stage_ms_host[9] gets
+ * the mean device time of {pose_begin, project_bin, tile_scan, bin_emit, tile_sort, raster_fwd, loss, raster_bwd,
+ * pose_finish} in ms.  The poses advance exactly as in gsb_tracker_run. */
+int gsb_tracker_profile(gsb_tracker* t, int n_iters, float* stage_ms_host);
 /* one forward only (render at the current poses; used for the GT re-render of geometry.py:69-135) */
 int gsb_tracker_forward(gsb_tracker* t);
 

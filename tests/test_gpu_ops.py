@@ -1,0 +1,319 @@
+"""GPU parity tests of the op-level boundary (gsplat.cuda._wrapper twins) against the CPU oracle.
+
+Shapes follow the dependency's own op tests (``test_projection``, ``test_isect`` with C,N = 3,1000 on a
+40x60 image and tile 16, ``test_rasterize_to_pixels``, ``test_sh``).  Tolerances are BASELINE.json's: tile ids /
+sorted keys / offsets bit-exact; rendered depth and alpha 1e-4 relative; gradients 1e-3 relative.
+"""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+import gsb_testutil as U
+from gsplatloc_b200 import synthetic as syn
+from oracle import gsplat_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ops(built_lib):
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from gsplatloc_b200 import ops as o
+    return o
+
+
+def _cloud(N=1000, C=3, W=60, H=40, seed=0, dtype=torch.float32):
+    arrs = syn.random_cloud(N, C, W, H, seed)
+    return [torch.tensor(a, dtype=dtype) for a in arrs]
+
+
+def _cuda(*ts):
+    return [t.cuda() if t is not None else None for t in ts]
+
+
+# ----------------------------------------------------------------------------------------------- projection
+@pytest.mark.parametrize("W,H,N,C", [(60, 40, 1000, 3), (320, 192, 5000, 2)])
+def test_projection_fwd(ops, W, H, N, C):
+    means, quats, scales, opac, view, Ks = _cloud(N, C, W, H, seed=1)
+    r_o, m_o, d_o, c_o = orc.project(means.double(), quats.double(), scales.double(), view.double(), Ks.double(), W, H)
+    radii, m2, dep, con, _ = ops.fully_fused_projection(*_cuda(means, None, quats, scales, view, Ks), W, H)
+    radii, m2, dep, con = radii.cpu(), m2.cpu(), dep.cpu(), con.cpu()
+    # the fp32 radius is a ceil(): allow it to differ by one where the fp64 value sits on an integer
+    both = (radii > 0) & (r_o > 0)
+    assert (both.sum() >= 0.98 * max((r_o > 0).sum(), 1)) and (((radii > 0) != (r_o > 0)).sum() <= 0.01 * N * C + 2)
+    assert (radii - r_o)[both].abs().max() <= 1
+    assert ((radii - r_o)[both] != 0).float().mean() < 0.01
+    assert both.sum() > 100
+    torch.testing.assert_close(m2[both].double(), m_o[both], rtol=1e-5, atol=1e-3)
+    torch.testing.assert_close(dep[both].double(), d_o[both], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(con[both].double(), c_o[both], rtol=2e-4, atol=1e-6)
+    culled = radii == 0
+    assert (m2[culled] == 0).all() and (dep[culled] == 0).all() and (con[culled] == 0).all()
+
+
+def test_projection_bwd_all_inputs(ops):
+    W, H, N, C = 96, 64, 600, 2
+    means, quats, scales, opac, view, Ks = _cloud(N, C, W, H, seed=2, dtype=torch.float64)
+    g = torch.Generator().manual_seed(3)
+    v_m2 = torch.randn(C, N, 2, generator=g, dtype=torch.float64)
+    v_d = torch.randn(C, N, generator=g, dtype=torch.float64)
+    v_c = torch.randn(C, N, 3, generator=g, dtype=torch.float64) * 1e-2
+    ins = [t.clone().requires_grad_(True) for t in (means, quats, scales, view)]
+    r_o, m_o, d_o, c_o = orc.project(ins[0], ins[1], ins[2], ins[3], Ks, W, H)
+    ((m_o * v_m2).sum() + (d_o * v_d).sum() + (c_o * v_c).sum()).backward()
+
+    cu = [t.float().cuda().requires_grad_(True) for t in (means, quats, scales, view)]
+    radii, m2, dep, con, _ = ops.fully_fused_projection(cu[0], None, cu[1], cu[2], cu[3], Ks.float().cuda(), W, H)
+    same = (radii.cpu() > 0) == (r_o > 0)
+    assert same.float().mean() > 0.995
+    # weight only Gaussians both sides keep, so the sums are over the same set
+    keep = ((radii.cpu() > 0) & (r_o > 0)).double()
+    for t in ins:
+        t.grad = None
+    r_o, m_o, d_o, c_o = orc.project(ins[0], ins[1], ins[2], ins[3], Ks, W, H)
+    ((m_o * v_m2 * keep[..., None]).sum() + (d_o * v_d * keep).sum() + (c_o * v_c * keep[..., None]).sum()).backward()
+    kc = keep.float().cuda()
+    ((m2 * v_m2.float().cuda() * kc[..., None]).sum() + (dep * v_d.float().cuda() * kc).sum()
+     + (con * v_c.float().cuda() * kc[..., None]).sum()).backward()
+    names = ["v_means", "v_quats", "v_scales", "v_viewmats"]
+    for n, a, b in zip(names, cu, ins):
+        ga, gb = a.grad.cpu().double(), b.grad
+        if n == "v_viewmats":
+            ga, gb = ga[:, :3, :], gb[:, :3, :]
+        assert U.rel_err(ga.numpy(), gb.numpy()) < 1e-3, (n, U.rel_err(ga.numpy(), gb.numpy()))
+
+
+# ----------------------------------------------------------------------------------------------- intersection
+def _isect_inputs(C, N, W, H, seed):
+    means, quats, scales, opac, view, Ks = _cloud(N, C, W, H, seed=seed)
+    radii, m2, dep, con = orc.project(means, quats, scales, view, Ks, W, H)
+    return m2.numpy(), radii.numpy(), dep.numpy()
+
+
+@pytest.mark.parametrize("method", ["tile", "radix"])
+@pytest.mark.parametrize("C,N,W,H", [(3, 1000, 60, 40), (1, 20000, 320, 192), (5, 3000, 130, 70)])
+def test_isect_bit_exact(ops, method, C, N, W, H):
+    m2, radii, dep = _isect_inputs(C, N, W, H, seed=4)
+    tw, th = math.ceil(W / 16), math.ceil(H / 16)
+    tpg_o, ids_o, fl_o = orc.isect_tiles(m2, radii, dep, 16, tw, th)
+    off_o = orc.isect_offset_encode(ids_o, C, tw, th)
+    tpg, ids, fl = ops.isect_tiles(torch.tensor(m2).cuda(), torch.tensor(radii).cuda(), torch.tensor(dep).cuda(), 16,
+                                   tw, th, method=method)
+    off = ops.isect_offset_encode(ids, C, tw, th)
+    assert ids.numel() == ids_o.size > 0
+    assert np.array_equal(tpg.cpu().numpy(), tpg_o)
+    assert np.array_equal(ids.cpu().numpy(), ids_o)
+    assert np.array_equal(fl.cpu().numpy(), fl_o)
+    assert np.array_equal(off.cpu().numpy(), off_o)
+
+
+def test_isect_unsorted_emission_order(ops):
+    C, N, W, H = 2, 500, 60, 40
+    m2, radii, dep = _isect_inputs(C, N, W, H, seed=5)
+    tpg_o, ids_o, fl_o = orc.isect_tiles(m2, radii, dep, 16, 4, 3, sort=False)
+    tpg, ids, fl = ops.isect_tiles(torch.tensor(m2).cuda(), torch.tensor(radii).cuda(), torch.tensor(dep).cuda(), 16,
+                                   4, 3, sort=False)
+    assert np.array_equal(ids.cpu().numpy(), ids_o) and np.array_equal(fl.cpu().numpy(), fl_o)
+
+
+@pytest.mark.parametrize("method", ["tile", "radix"])
+def test_isect_ties_and_empty(ops, method):
+    # bit-identical depths in one tile: the stable order (lower flat index first) must survive
+    m2 = np.array([[[20.0, 20.0], [10.0, 10.0], [21.0, 19.0], [22.0, 22.0]]], dtype=np.float32)
+    radii = np.array([[6, 6, 6, 6]], dtype=np.int32)
+    dep = np.array([[2.0, 1.0, 2.0, 2.0]], dtype=np.float32)
+    tpg_o, ids_o, fl_o = orc.isect_tiles(m2, radii, dep, 16, 4, 4)
+    tpg, ids, fl = ops.isect_tiles(torch.tensor(m2).cuda(), torch.tensor(radii).cuda(), torch.tensor(dep).cuda(), 16,
+                                   4, 4, method=method)
+    assert np.array_equal(ids.cpu().numpy(), ids_o) and np.array_equal(fl.cpu().numpy(), fl_o)
+    # nothing visible
+    z = torch.zeros(2, 5, 2).cuda()
+    tpg, ids, fl = ops.isect_tiles(z, torch.zeros(2, 5, dtype=torch.int32).cuda(), torch.ones(2, 5).cuda(), 16, 3, 2,
+                                   method=method)
+    assert ids.numel() == 0 and fl.numel() == 0 and int(tpg.sum()) == 0
+    off = ops.isect_offset_encode(ids, 2, 3, 2)
+    assert off.shape == (2, 2, 3) and int(off.abs().sum()) == 0
+
+
+def test_isect_big_bins_sort_in_global_memory(ops):
+    # > 4096 Gaussians in one tile exercises the out-of-shared-memory branch of the tile sort
+    rng = np.random.default_rng(6)
+    N = 6000
+    m2 = (rng.uniform(2, 14, (1, N, 2))).astype(np.float32)
+    radii = np.full((1, N), 1, dtype=np.int32)
+    dep = rng.uniform(0.5, 5.0, (1, N)).astype(np.float32)
+    dep[0, ::7] = dep[0, 0]  # many ties
+    tpg_o, ids_o, fl_o = orc.isect_tiles(m2, radii, dep, 16, 2, 2)
+    tpg, ids, fl = ops.isect_tiles(torch.tensor(m2).cuda(), torch.tensor(radii).cuda(), torch.tensor(dep).cuda(), 16,
+                                   2, 2, method="tile")
+    assert np.array_equal(ids.cpu().numpy(), ids_o) and np.array_equal(fl.cpu().numpy(), fl_o)
+
+
+# ----------------------------------------------------------------------------------------------- rasterisation
+def _raster_setup(C, N, W, H, D, seed, opaque=False):
+    means, quats, scales, opac, view, Ks = _cloud(N, C, W, H, seed=seed, dtype=torch.float64)
+    if opaque:
+        opac = torch.ones_like(opac)
+    radii, m2, dep, con = orc.project(means, quats, scales * 3, view, Ks, W, H)
+    # round-trip through fp32 so both sides see bit-identical inputs
+    m2, dep, con = m2.float(), dep.float(), con.float()
+    tw, th = math.ceil(W / 16), math.ceil(H / 16)
+    tpg, ids, fl = orc.isect_tiles(m2.numpy(), radii.numpy(), dep.numpy(), 16, tw, th)
+    offs = orc.isect_offset_encode(ids, C, tw, th)
+    g = torch.Generator().manual_seed(seed)
+    colors = torch.rand(C, N, D, generator=g)
+    op = opac.float()[None].expand(C, N).contiguous()
+    return m2, con, colors, op, offs, fl, tw, th
+
+
+@pytest.mark.parametrize("D", [1, 3, 4, 8])
+@pytest.mark.parametrize("opaque", [False, True])
+def test_rasterize_fwd_bwd(ops, D, opaque):
+    C, N, W, H = 2, 800, 100, 70
+    m2, con, colors, op, offs, fl, tw, th = _raster_setup(C, N, W, H, D, seed=7, opaque=opaque)
+    dt = torch.float64
+    ins_o = [t.to(dt).clone().requires_grad_(True) for t in (m2, con, colors, op)]
+    rc_o, ra_o, last_o = orc.rasterize(*ins_o, W, H, 16, offs, fl)
+    g = torch.Generator().manual_seed(8)
+    v_rc, v_ra = torch.randn(C, H, W, D, generator=g), torch.randn(C, H, W, 1, generator=g)
+    ((rc_o * v_rc.to(dt)).sum() + (ra_o * v_ra.to(dt)).sum()).backward()
+
+    ins = [t.cuda().requires_grad_(True) for t in (m2, con, colors, op)]
+    rc, ra = ops.rasterize_to_pixels(*ins, W, H, 16, torch.tensor(offs).cuda(), torch.tensor(fl).cuda())
+    assert U.rel_err(rc.detach().cpu().numpy(), rc_o.detach().numpy()) < 1e-4
+    assert U.rel_err(ra.detach().cpu().numpy(), ra_o.detach().numpy()) < 1e-4
+    ((rc * v_rc.cuda()).sum() + (ra * v_ra.cuda()).sum()).backward()
+    for n, a, b in zip(["v_means2d", "v_conics", "v_colors", "v_opacities"], ins, ins_o):
+        e = U.rel_err(a.grad.cpu().numpy(), b.grad.numpy())
+        assert e < 1e-3, (n, e)
+
+
+def test_rasterize_backgrounds(ops):
+    C, N, W, H, D = 1, 500, 64, 48, 3
+    m2, con, colors, op, offs, fl, tw, th = _raster_setup(C, N, W, H, D, seed=9)
+    bg = torch.tensor([[0.2, 0.5, 0.9]])
+    rc_o, ra_o, _ = orc.rasterize(m2, con, colors, op, W, H, 16, offs, fl)
+    rc_o = rc_o + (1 - ra_o) * bg[:, None, None, :]
+    rc, ra = ops.rasterize_to_pixels(*_cuda(m2, con, colors, op), W, H, 16, torch.tensor(offs).cuda(),
+                                     torch.tensor(fl).cuda(), backgrounds=bg.cuda())
+    assert U.rel_err(rc.cpu().numpy(), rc_o.numpy()) < 1e-4
+
+
+# ----------------------------------------------------------------------------------------------- SH
+def test_spherical_harmonics_deg1(ops):
+    g = torch.Generator().manual_seed(10)
+    n = 777
+    dirs = torch.randn(n, 3, generator=g, dtype=torch.float64)
+    coeffs = torch.randn(n, 4, 3, generator=g, dtype=torch.float64)
+    masks = torch.rand(n, generator=g) > 0.2
+    v = torch.randn(n, 3, generator=g, dtype=torch.float64)
+    for deg in (0, 1):
+        do, co = dirs.clone().requires_grad_(True), coeffs.clone().requires_grad_(True)
+        out_o = orc.spherical_harmonics(deg, do, co, masks)
+        (out_o * v).sum().backward()
+        dc, cc = dirs.float().cuda().requires_grad_(True), coeffs.float().cuda().requires_grad_(True)
+        out = ops.spherical_harmonics(deg, dc, cc, masks.cuda())
+        (out * v.float().cuda()).sum().backward()
+        torch.testing.assert_close(out.detach().cpu().double(), out_o.detach(), rtol=1e-5, atol=1e-6)
+        torch.testing.assert_close(cc.grad.cpu().double(), co.grad, rtol=1e-5, atol=1e-6)
+        if deg == 1:
+            torch.testing.assert_close(dc.grad.cpu().double(), do.grad, rtol=1e-4, atol=1e-5)
+
+
+# ----------------------------------------------------------------------------------------------- rasterization()
+@pytest.mark.parametrize("render_mode", ["ED", "RGB+ED", "D", "RGB"])
+def test_rasterization_matches_oracle(ops, render_mode):
+    from gsplatloc_b200 import rasterization
+    fp = U.frame(U.SMALL_CAM, stride=2, seed=11)
+    dt = torch.float64
+    means, quats, scales, opac = U.map_tensors(fp, dt)
+    N = means.shape[0]
+    q0, t0 = U.offgrid_pose(fp, dt)
+    view = torch.linalg.inv(orc.pose_to_c2w(q0, t0))[None]
+    K = torch.tensor(fp.K, dtype=dt)[None]
+    g = torch.Generator().manual_seed(12)
+    rgb = torch.rand(N, 3, generator=g, dtype=dt)
+    sh = torch.cat([((rgb - 0.5) / orc.SH_C0)[:, None, :], torch.zeros(N, 3, 3, dtype=dt)], 1)  # model.py:169-175
+    vo = view.clone().requires_grad_(True)
+    rc_o, ra_o, meta_o = orc.rasterization(means, quats, scales, opac, sh, vo, K, fp.W, fp.H, sh_degree=1,
+                                           render_mode=render_mode)
+    v_rc = torch.randn(rc_o.shape, generator=g, dtype=dt)
+    (rc_o * v_rc).sum().backward()
+
+    vc = view.float().cuda().requires_grad_(True)
+    rc, ra, meta = rasterization(means.float().cuda(), quats.float().cuda(), scales.float().cuda(),
+                                 opac.float().cuda(), sh.float().cuda(), vc, K.float().cuda(), fp.W, fp.H,
+                                 sh_degree=1, packed=False, absgrad=False, sparse_grad=False, far_plane=1e10,
+                                 near_plane=1e-2, render_mode=render_mode, rasterize_mode="classic")
+    assert rc.shape == rc_o.shape and ra.shape == ra_o.shape
+    assert U.rel_err(rc.detach().cpu().numpy(), rc_o.detach().numpy()) < 1e-4
+    assert U.rel_err(ra.detach().cpu().numpy(), ra_o.detach().numpy()) < 1e-4
+    (rc * v_rc.float().cuda()).sum().backward()
+    e = U.rel_err(vc.grad[:, :3].cpu().numpy(), vo.grad[:, :3].numpy())
+    assert e < 1e-3, e
+    for k in ("radii", "means2d", "depths", "conics", "opacities", "tile_width", "tile_height", "tiles_per_gauss",
+              "isect_ids", "flatten_ids", "isect_offsets", "width", "height", "tile_size", "n_cameras"):
+        assert k in meta
+
+
+def test_rasterization_pose_gradient_through_inverse(ops):
+    """The reference's pose path: viewmats = linalg.inv(c2w(q, t)) (model.py:202), loss on channel 3 of RGB+ED."""
+    from gsplatloc_b200 import rasterization
+    fp = U.frame(U.SMALL_CAM, stride=2, seed=13)
+    dt = torch.float64
+    means, quats, scales, opac = U.map_tensors(fp, dt)
+    gt = torch.tensor(fp.src_depth, dtype=dt)
+    K = torch.tensor(fp.K, dtype=dt)
+    q0, t0 = U.offgrid_pose(fp, dt)
+    q, t = q0.clone().requires_grad_(True), t0.clone().requires_grad_(True)
+    tot, *_ = orc.pose_loss(q, t, means, quats, scales, opac, gt, K, fp.W, fp.H)
+    tot.backward()
+
+    qc, tc = q0.float().cuda().requires_grad_(True), t0.float().cuda().requires_grad_(True)
+    qn = qc / qc.norm().clamp_min(1e-12)
+    w, x, y, z = qn.unbind(0)
+    R = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y),
+                     2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x),
+                     2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]).reshape(3, 3)
+    c2w = torch.cat([torch.cat([R, tc[:, None]], 1), torch.tensor([[0.0, 0, 0, 1]]).cuda()], 0)
+    N = means.shape[0]
+    sh = torch.zeros(N, 4, 3).cuda()
+    rc, ra, _ = rasterization(means.float().cuda(), quats.float().cuda(), scales.float().cuda(), opac.float().cuda(),
+                              sh, torch.linalg.inv(c2w)[None], K.float().cuda()[None], fp.W, fp.H, sh_degree=1,
+                              packed=False, render_mode="RGB+ED")
+    assert rc.shape[-1] == 4
+    d = rc[0, :, :, 3]
+    m = (d != 0).float()
+    A, B = d * m, gt.float().cuda() * m
+    import torch.nn.functional as F
+    kx = torch.tensor([[-1.0, 0.0, 1.0], [-2.0, 0.0, 2.0], [-1.0, 0.0, 1.0]]).cuda() / 8.0
+    k = torch.stack([kx, kx.t()])[:, None]
+
+    def sob(img):
+        gg = F.conv2d(F.pad(img[None, None], (1, 1, 1, 1), mode="replicate"), k)
+        return torch.sqrt(gg[:, 0] ** 2 + gg[:, 1] ** 2 + 1e-6)
+    loss = 0.8 * (A - B).abs().mean() + 0.2 * (sob(A) - sob(B)).abs().mean()
+    loss.backward()
+    assert abs(float(loss) - float(tot)) / float(tot) < 1e-4
+    assert U.rel_err(qc.grad.cpu().numpy(), q.grad.numpy()) < 1e-3
+    assert U.rel_err(tc.grad.cpu().numpy(), t.grad.numpy()) < 1e-3
+
+
+# ----------------------------------------------------------------------------------------------- fused loss
+@pytest.mark.parametrize("W,H", [(160, 96), (37, 21), (64, 8)])
+def test_depth_edge_loss_kernel(ops, W, H):
+    from gsplatloc_b200 import losses
+    g = torch.Generator().manual_seed(14)
+    d = torch.rand(H, W, generator=g, dtype=torch.float64) * 3 + 0.5
+    d[torch.rand(H, W, generator=g) < 0.1] = 0.0          # holes: the trainer's mask (gs_trainer_total.py:109)
+    gt = d + torch.randn(H, W, generator=g, dtype=torch.float64) * 0.05
+    do = d.clone().requires_grad_(True)
+    tot, Ld, Ls, _ = orc.losses(do, gt)
+    tot.backward()
+    Ld_c, Ls_c, v = losses.depth_edge_loss(d.float().cuda()[None], gt.float().cuda(), depth_lambda=0.8)
+    assert abs(float(Ld_c[0]) - float(Ld)) / float(Ld) < 1e-5
+    assert abs(float(Ls_c[0]) - float(Ls)) / float(Ls) < 1e-5
+    assert U.rel_err(v[0].cpu().numpy(), do.grad.numpy()) < 1e-4

@@ -1,0 +1,238 @@
+"""GPU parity tests of the device-resident pose loop (the inner loop of Runner.train, gs_trainer_total.py:78-267)
+against the CPU oracle: intermediates bit-exact, render 1e-4, pose gradient 1e-3, converged pose 1e-3 m."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+import gsb_testutil as U
+from oracle import gsplat_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def gsb(built_lib):
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import gsplatloc_b200
+    return gsplatloc_b200
+
+
+def _tracker(gsb, fp, c2w0, gt, C=1, **cfg):
+    means, quats, scales, opac = U.map_tensors(fp, torch.float32, "cuda")
+    trk = gsb.PoseTracker(fp.W, fp.H, C, gsb.TrackerConfig(**cfg))
+    trk.set_map(means, quats, scales, opac)
+    trk.set_observation(torch.as_tensor(gt, dtype=torch.float32).cuda(), fp.K)
+    trk.set_poses(c2w0, fp.src_c2w)
+    return trk
+
+
+def _oracle_step(fp, c2w0, gt, dt=torch.float64):
+    means, quats, scales, opac = U.map_tensors(fp, dt)
+    q = torch.tensor(orc.rotmat_to_quat(c2w0[:3, :3]), dtype=dt).requires_grad_(True)
+    t = torch.tensor(c2w0[:3, 3], dtype=dt).requires_grad_(True)
+    out = orc.pose_loss(q, t, means, quats, scales, opac, torch.as_tensor(gt, dtype=dt), torch.tensor(fp.K, dtype=dt),
+                        fp.W, fp.H)
+    out[0].backward()
+    return q, t, out
+
+
+def _start_pose(fp):
+    q0, t0 = U.offgrid_pose(fp, torch.float64)
+    return orc.pose_to_c2w(q0, t0).numpy()
+
+
+@pytest.mark.parametrize("cam,stride,seed", [(U.SMALL_CAM, 2, 42), (U.MID_CAM, 2, 3), (U.SMALL_CAM, 1, 5)])
+def test_one_iteration_matches_oracle(gsb, cam, stride, seed):
+    fp = U.frame(cam, stride=stride, seed=seed)
+    c2w0 = _start_pose(fp)
+    trk = _tracker(gsb, fp, c2w0, fp.src_depth, early_stop=False)
+    trk.run(1, poll_every=0, use_graph=False)
+    st = trk.states()[0]
+    q, t, (tot, Ld, Ls, Ln, d, a, meta) = _oracle_step(fp, c2w0, fp.src_depth)
+    d_gpu, a_gpu = trk.render()
+    assert U.rel_err(d_gpu[0].cpu().numpy(), d.detach().numpy()) < 1e-4
+    assert U.rel_err(a_gpu[0].cpu().numpy(), a.detach().numpy()) < 1e-4
+    assert abs(st["depth_loss"] - float(Ld)) / float(Ld) < 1e-4
+    assert abs(st["edge_loss"] - float(Ls)) / float(Ls) < 1e-4
+    assert abs(st["loss"] - float(tot)) / float(tot) < 1e-4
+    assert U.rel_err(st["g_q"], q.grad.numpy()) < 1e-3, (st["g_q"], q.grad)
+    assert U.rel_err(st["g_t"], t.grad.numpy()) < 1e-3, (st["g_t"], t.grad)
+    eT, eR = orc.pose_errors(c2w0, fp.src_c2w)
+    assert abs(st["eT"] - eT) < 1e-5 and abs(st["eR"] - eR) < 1e-2
+    trk.close()
+
+
+def test_intermediates_bit_exact_given_the_kernel_projection(gsb):
+    """tile ids / sorted order / offsets: bit-exact against the oracle's intersection + stable sort when both
+    start from the SAME projected means2d / radii / depths (the kernel's own records)."""
+    fp = U.frame(U.MID_CAM, stride=2, seed=9)
+    c2w0 = _start_pose(fp)
+    trk = _tracker(gsb, fp, c2w0, fp.src_depth, early_stop=False)
+    trk.forward()
+    fl, off, rec = trk.debug_tensors()
+    rec = rec.cpu().numpy()
+    radii = rec[:, 7].view(np.int32).copy()[None]
+    m2 = rec[None, :, 0:2].copy()
+    m2[radii == 0] = 0
+    dep = rec[None, :, 2].copy()
+    tw, th = math.ceil(fp.W / 16), math.ceil(fp.H / 16)
+    tpg_o, ids_o, fl_o = orc.isect_tiles(m2, radii, dep, 16, tw, th)
+    off_o = orc.isect_offset_encode(ids_o, 1, tw, th).reshape(-1)
+    assert trk.counters()["n_isects"] == ids_o.size
+    assert np.array_equal(fl.cpu().numpy(), fl_o)
+    assert np.array_equal(off.cpu().numpy()[:-1], off_o) and int(off[-1]) == ids_o.size
+    # and the projection itself agrees with the oracle's within fp32 rounding
+    means, quats, scales, opac = U.map_tensors(fp, torch.float64)
+    view = torch.linalg.inv(torch.tensor(c2w0))[None]
+    r_o, m_o, d_o, c_o = orc.project(means, quats, scales, view, torch.tensor(fp.K, dtype=torch.float64)[None], fp.W, fp.H)
+    both = (radii[0] > 0) & (r_o[0].numpy() > 0)
+    assert both.mean() > 0.5 and ((radii[0] > 0) != (r_o[0].numpy() > 0)).mean() < 1e-3
+    assert np.abs(radii[0][both] - r_o[0].numpy()[both]).max() <= 1
+    np.testing.assert_allclose(rec[both, 0:2], m_o[0].numpy()[both], rtol=1e-5, atol=1e-3)
+    np.testing.assert_allclose(rec[both, 2], d_o[0].numpy()[both], rtol=1e-5)
+    np.testing.assert_allclose(rec[both, 4:7], c_o[0].numpy()[both], rtol=2e-4, atol=1e-7)
+    trk.close()
+
+
+def test_loop_tracks_the_oracle_loop(gsb):
+    """20 Adam iterations: the pose trajectory stays on the oracle's (fp32 oracle, same arithmetic order not
+    guaranteed, so the bound is loose on the pose and tight on the loss)."""
+    fp = U.frame(U.SMALL_CAM, stride=2, seed=7, trans_cm=1.0, rot_deg=0.5)
+    gt = U.oracle_gt_depth(fp, torch.float32).numpy()
+    c2w0 = fp.tar_c2w.astype(np.float64)
+    n = 20
+    trk = _tracker(gsb, fp, c2w0, gt, early_stop=False, max_steps=1000)
+    trk.run(n, poll_every=0, use_graph=True)
+    hist = trk.history(0)
+    st = trk.states()[0]
+    dt = torch.float32
+    means, quats, scales, opac = U.map_tensors(fp, dt)
+    res = orc.pose_opt_loop(torch.tensor(orc.rotmat_to_quat(c2w0[:3, :3]), dtype=dt), torch.tensor(c2w0[:3, 3], dtype=dt),
+                            means, quats, scales, opac, torch.tensor(gt), torch.tensor(fp.K), fp.W, fp.H,
+                            c2w_gt=fp.src_c2w, max_steps=1000, n_steps=n, early_stop=False)
+    assert hist.shape[0] == n
+    lo = np.array([h[0] for h in res["history"]])
+    assert np.abs(hist[:, 0] - lo).max() / lo.max() < 2e-3, (hist[:, 0], lo)
+    assert np.abs(st["t"] - res["t"].numpy()).max() < 2e-4
+    assert np.abs(st["q"] - res["quat"].numpy()).max() < 2e-4
+    trk.close()
+
+
+def test_graph_and_eager_are_identical_and_deterministic(gsb):
+    fp = U.frame(U.SMALL_CAM, stride=2, seed=21)
+    c2w0 = _start_pose(fp)
+    outs = []
+    for use_graph in (False, True, True):
+        trk = _tracker(gsb, fp, c2w0, fp.src_depth, early_stop=False)
+        trk.run(15, poll_every=5, use_graph=use_graph)
+        st = trk.states()[0]
+        outs.append(np.concatenate([st["q"], st["t"], [st["loss"]]]))
+        trk.close()
+    assert np.array_equal(outs[0].view(np.uint32), outs[1].view(np.uint32))
+    assert np.array_equal(outs[1].view(np.uint32), outs[2].view(np.uint32))
+
+
+def test_converges_to_ground_truth_pose(gsb):
+    """Converged ATE within 1e-3 m of the known synthetic delta (BASELINE.json north_star)."""
+    fp = U.frame(U.MID_CAM, stride=1, seed=31, trans_cm=1.5, rot_deg=0.7)
+    # observation = splat render of the source frame's own points from its own pose (dataset.py:362-372)
+    means_s = torch.tensor(fp.src_points).cuda()
+    Ns = means_s.shape[0]
+    gtr = gsb.PoseTracker(fp.W, fp.H, 1)
+    gtr.set_map(means_s, torch.tensor([[1.0, 0, 0, 0]]).repeat(Ns, 1).cuda(), torch.tensor(fp.src_scales).cuda(),
+                torch.ones(Ns).cuda())
+    gtr.set_observation(torch.zeros(fp.H, fp.W).cuda(), fp.K)
+    gtr.set_poses(fp.src_c2w)
+    gtr.forward()
+    gt, _ = gtr.render()
+    gtr.close()
+    trk = _tracker(gsb, fp, fp.tar_c2w, gt[0], max_steps=1000, early_stop=True, patience=100)
+    eT0, eR0 = orc.pose_errors(fp.tar_c2w, fp.src_c2w)
+    res = trk.run(1000, poll_every=50)
+    st = trk.states()[0]
+    assert st["best_eT"] < 1e-3 and st["best_eT"] < 0.1 * eT0, (eT0, st["best_eT"])
+    assert st["best_eR"] < 0.05 and st["best_eR"] < 0.2 * eR0, (eR0, st["best_eR"])
+    assert st["stopped"] == 1 and res["iters"] < 1000, "the early stop (gs_trainer_total.py:160-185) must fire"
+    trk.close()
+
+
+def test_early_stop_bookkeeping_matches_reference_rule(gsb):
+    """step > warmup: best tracking; counter >= patience: stop BEFORE the optimiser step (gs_trainer_total.py:160-185,
+    245-263). Replays the rule on the recorded loss history."""
+    fp = U.frame(U.SMALL_CAM, stride=2, seed=17, trans_cm=0.5, rot_deg=0.2)
+    trk = _tracker(gsb, fp, fp.tar_c2w, fp.src_depth, max_steps=300, early_stop=True, patience=12, warmup=10)
+    trk.run(300, poll_every=10)
+    st = trk.states()[0]
+    hist = trk.history(0)
+    best, counter, stop_at, best_iter = np.inf, 0, None, -1
+    for step, row in enumerate(hist):
+        if step > 10:
+            if row[0] < best:
+                best, counter, best_iter = row[0], 0, step
+            else:
+                counter += 1
+        if counter >= 12:
+            stop_at = step
+            break
+    assert stop_at is not None and st["stopped"] == 1
+    assert hist.shape[0] == stop_at + 1
+    assert st["best_iter"] == best_iter and st["best_loss"] == np.float32(best)
+    assert st["adam_step"] == stop_at, "the gradient of the stopping iteration is discarded"
+    trk.close()
+
+
+def test_hypotheses_are_independent(gsb):
+    """C pose hypotheses through the camera axis give exactly what C single-camera runs give."""
+    fp = U.frame(U.SMALL_CAM, stride=2, seed=23)
+    rng = np.random.default_rng(0)
+    poses = []
+    for c in range(3):
+        p = _start_pose(fp).copy()
+        p[:3, 3] += rng.normal(0, 0.01, 3)
+        poses.append(p)
+    multi = _tracker(gsb, fp, np.stack(poses), fp.src_depth, C=3, early_stop=False)
+    multi.run(8, poll_every=0)
+    ms = multi.states()
+    for c in range(3):
+        one = _tracker(gsb, fp, poses[c], fp.src_depth, early_stop=False)
+        one.run(8, poll_every=0)
+        s = one.states()[0]
+        assert np.allclose(ms[c]["q"], s["q"], atol=1e-6) and np.allclose(ms[c]["t"], s["t"], atol=1e-6)
+        assert abs(ms[c]["loss"] - s["loss"]) < 1e-6 * max(1.0, s["loss"])
+        one.close()
+    multi.close()
+
+
+def test_full_size_properties_replica_200k(gsb):
+    """BASELINE.json config 2 (1200x680, ~200k Gaussians): too big for the oracle, so check size-independent
+    properties: sorted tile ranges, offsets monotone and closed, alpha in [0,1], depth within the scene range,
+    loss decreasing, repeatable bits."""
+    from gsplatloc_b200 import synthetic as syn
+    fp = syn.make_frame_pair(syn.REPLICA, stride=2, seed=42)
+    assert 190_000 < fp.tar_points.shape[0] < 210_000
+    losses = []
+    for rep in range(2):
+        trk = _tracker(gsb, fp, fp.tar_c2w, fp.src_depth, early_stop=False)
+        trk.run(30, poll_every=0)
+        st = trk.states()[0]
+        losses.append(st["loss"])
+        if rep == 0:
+            hist = trk.history(0)
+            fl, off, rec = trk.debug_tensors()
+            M = trk.counters()["n_isects"]
+            off = off.cpu().numpy().astype(np.int64)
+            assert off[0] == 0 and off[-1] == M and np.all(np.diff(off) >= 0)
+            dbits = rec[:, 2].contiguous().view(torch.int32)[fl.long()].cpu().numpy().astype(np.int64)
+            tile_of = np.repeat(np.arange(off.size - 1), np.diff(off))
+            key = (tile_of << 32) | dbits
+            assert np.all(np.diff(key) >= 0), "every tile range sorted by depth bits"
+            d, a = trk.render()
+            assert float(a.min()) >= 0 and float(a.max()) <= 1.0
+            dd = d[a > 0.5]
+            assert float(dd.min()) > 0.2 and float(dd.max()) < 12.0
+            assert hist[-1, 0] < hist[0, 0] and hist[-1, 4] < hist[0, 4], "loss and eT go down"
+        trk.close()
+    assert np.float32(losses[0]).view(np.uint32) == np.float32(losses[1]).view(np.uint32)
