@@ -84,15 +84,16 @@ void launch_isect_count(int CN, const float* means2d, const int* radii, int tile
                                                          tiles_per_gauss);
 }
 
-size_t cumsum_workspace_bytes(int CN) {
-    size_t bytes = 0;
-    cub::DeviceScan::InclusiveSum((void*)nullptr, bytes, (const int*)nullptr, (int64_t*)nullptr, CN);
-    return bytes;
-}
-
 struct IntToI64 {
     __host__ __device__ int64_t operator()(int v) const { return (int64_t)v; }
 };
+
+size_t cumsum_workspace_bytes(int CN) {
+    size_t bytes = 0;
+    cub::TransformInputIterator<int64_t, IntToI64, const int*> it((const int*)nullptr, IntToI64());
+    cub::DeviceScan::InclusiveSum((void*)nullptr, bytes, it, (int64_t*)nullptr, CN);
+    return bytes + 256;
+}
 
 cudaError_t launch_cumsum(int CN, const int* tiles_per_gauss, int64_t* cum, void* ws, size_t ws_bytes,
                           cudaStream_t st) {
