@@ -221,10 +221,47 @@ __device__ __forceinline__ void quat_to_rotmat_vjp(const float* __restrict__ q, 
     vq[0] = (gw - d * w) * inv; vq[1] = (gx - d * x) * inv; vq[2] = (gy - d * y) * inv; vq[3] = (gz - d * z) * inv;
 }
 
+// exp(-sigma) as one MUFU.EX2 (flush-to-zero: results below 2^-126 become 0, far under the 1/255 alpha test) and
+// 1/x as one MUFU.RCP for x in [1e-3, 1] — what the reference's --use_fast_math build does.
+__device__ __forceinline__ float exp_neg_fast(float sigma) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(sigma * -1.4426950408889634f));
+    return y;
+}
+__device__ __forceinline__ float rcp_fast(float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
+}
+
+// Conservative 8-bit "patch mask" of one Gaussian inside a 16x16 tile whose first pixel is (tile_x0, tile_y0).
+// A warp of the raster kernels owns an 8x4 pixel patch: warp w covers columns 8*(w&1)..+7 and rows 4*(w>>1)..+3.
+// Bit w is set when the alpha >= 1/255 ellipse of the Gaussian (sigma <= ln(255*opacity), A.4) can reach a pixel
+// centre of that patch; tested with the ellipse's axis-aligned extents sqrt(2*tau*Cov_xx), sqrt(2*tau*Cov_yy)
+// (Cov = conic^-1) plus slack, so a cleared bit PROVES that every pixel of the patch fails the A.4 alpha test.
+// The per-pixel test stays exact; the mask only removes work.
+__device__ __forceinline__ unsigned patch_mask(float mx, float my, float a, float b, float c, float opac,
+                                               float tile_x0, float tile_y0) {
+    const float tau = __logf(255.f * opac) + 0.02f;
+    if (tau <= 0.f) return 0u;                 // opacity below 1/255: no pixel passes
+    const float det = a * c - b * b;
+    if (!(tau > 0.f) || !(det > 0.f) || !(a > 0.f) || !(c > 0.f)) return 0xffu;  // NaN / degenerate: no culling
+    const float k = __fdividef(2.f * tau, det);
+    const float kc = k * c, ka = k * a;        // squared half extents; sqrt(x) = x * rsqrt(x) (MUFU, 2 ulp)
+    const float hx = kc * rsqrtf(kc) * 1.0002f + 0.02f, hy = ka * rsqrtf(ka) * 1.0002f + 0.02f;
+    if (!(fabsf(mx) + fabsf(my) + hx + hy < 3e38f)) return 0xffu;
+    const float lx = mx - hx - tile_x0, ux = mx + hx - tile_x0;  // extents relative to the tile origin
+    const float ly = my - hy - tile_y0, uy = my + hy - tile_y0;
+    const unsigned xm = ((ux >= 0.5f && lx <= 7.5f) ? 1u : 0u) | ((ux >= 8.5f && lx <= 15.5f) ? 2u : 0u);
+    const unsigned ys = ((uy >= 0.5f && ly <= 3.5f) ? 1u : 0u) | ((uy >= 4.5f && ly <= 7.5f) ? 4u : 0u) |
+                        ((uy >= 8.5f && ly <= 11.5f) ? 16u : 0u) | ((uy >= 12.5f && ly <= 15.5f) ? 64u : 0u);
+    return xm * ys;                            // xm (2 bits) replicated at bit 2r for every reachable patch row r
 }
 
 }  // namespace gsb

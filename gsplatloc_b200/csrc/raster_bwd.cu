@@ -1,7 +1,8 @@
 // Back-to-front replay of the compositing and its VJP (Appendix A.5 / A.6).
 //
-// One 256-thread block per (camera, 16x16 tile); each warp owns an 8x4 pixel patch.  For every sorted Gaussian the
-// per-pixel gradient terms (v_xy[2], v_conic[3], v_colour[CDIM], v_opacity) are summed over the warp with a
+// One 256-thread block per (camera, 16x16 tile); each warp owns an 8x4 pixel patch and walks only the staged
+// Gaussians whose 8-bit patch mask (common.cuh) says their alpha >= 1/255 ellipse can reach that patch.  For every
+// such Gaussian the per-pixel gradient terms (v_xy[2], v_conic[3], v_colour[CDIM], v_opacity) are summed over the warp with a
 // halving butterfly (log2 steps, 9 shuffles for 8 values instead of 40).
 //   LIFT = true (tracker): the warp sums land in a per-warp slot of shared memory (no atomics, fixed order =
 //       deterministic); after each batch one thread per Gaussian adds the 8 warp slots and pushes the 6 numbers
@@ -77,6 +78,38 @@ struct BwdCfg {
     static constexpr int NV = (6 + CDIM <= 8) ? 8 : 16;                    // reduced values (padded)
 };
 
+// Everything the out-of-line lift needs, staged once per block in shared memory.
+struct LiftCtx {
+    Cam cam;
+    const float* means;
+    const float* quats;
+    const float* scales;
+    int W, H, N, cam_index;
+    float eps2d;
+};
+
+// A.6 for one staged Gaussian: the six tile-summed numbers (v_xy, v_conic, v_depth) -> 12 pose-gradient numbers,
+// accumulated into this thread's column of s_pose[12][BWD_BATCH].  Out of line on purpose: the camera, the
+// re-projection temporaries and the accumulators must not compete for registers with the replay loop.
+__device__ __noinline__ void lift_to_pose(const LiftCtx* __restrict__ ctx, int flat_id, float g0, float g1, float g2,
+                                          float g3, float g4, float g5, float* __restrict__ pose_col) {
+    const Cam camera = ctx->cam;
+    const int n = flat_id - ctx->cam_index * ctx->N;
+    const float mean[3] = {__ldg(ctx->means + n * 3), __ldg(ctx->means + n * 3 + 1), __ldg(ctx->means + n * 3 + 2)};
+    const float4 q4 = __ldg(reinterpret_cast<const float4*>(ctx->quats) + n);
+    const float q[4] = {q4.x, q4.y, q4.z, q4.w};
+    const float sc[3] = {__ldg(ctx->scales + n * 3), __ldg(ctx->scales + n * 3 + 1), __ldg(ctx->scales + n * 3 + 2)};
+    Proj p; float S[6], Sc[6];
+    project_gaussian(camera, mean, q, sc, ctx->W, ctx->H, ctx->eps2d, -1e30f, 1e30f, -1.f, p, S, Sc);
+    float v_pc[3], vS[6], acc[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) acc[k] = 0.f;
+    project_vjp(camera, p, Sc, g0, g1, g2, g3, g4, g5, v_pc, vS);
+    pose_accumulate(camera, mean, S, v_pc, vS, acc, acc + 9);
+#pragma unroll
+    for (int k = 0; k < 12; ++k) pose_col[k * BWD_BATCH] += acc[k];
+}
+
 template <int CDIM, bool PACKED, bool LIFT>
 __global__ void __launch_bounds__(256) raster_bwd_kernel(
     int C, int N, int W, int H, int tile_w, int tile_h, const float4* __restrict__ rec,
@@ -94,8 +127,10 @@ __global__ void __launch_bounds__(256) raster_bwd_kernel(
     __shared__ __align__(16) float sm[BWD_BATCH * RS];
     __shared__ int s_id[BWD_BATCH];
     __shared__ __align__(16) float s_acc[LIFT ? 8 * BWD_BATCH * 6 : 4];
-    __shared__ float s_red[12 * 8];
+    __shared__ float s_pose[LIFT ? 12 * BWD_BATCH : 1];
+    __shared__ LiftCtx s_ctx;
     __shared__ int s_max[8];
+    __shared__ unsigned char s_mask[BWD_BATCH];
 
     const int cam = blockIdx.z;
     if (stop && stop[cam]) return;
@@ -104,12 +139,22 @@ __global__ void __launch_bounds__(256) raster_bwd_kernel(
     const int j = blockIdx.x * 16 + (wid & 1) * 8 + (lane & 7);
     const int i = blockIdx.y * 16 + (wid >> 1) * 4 + (lane >> 3);
     const float px = (float)j + 0.5f, py = (float)i + 0.5f;
+    const float tile_x0 = (float)(blockIdx.x * 16), tile_y0 = (float)(blockIdx.y * 16);
     const bool inside = (i < H) && (j < W);
     const size_t pix = ((size_t)cam * H + min(i, H - 1)) * W + min(j, W - 1);
     const int n_isects = n_isects_dev ? *n_isects_dev : n_isects_host;
     const int bin = cam * tile_w * tile_h + tile_id;
     const int range_start = tile_offsets[bin];
     const int range_end = (bin == C * tile_w * tile_h - 1) ? n_isects : tile_offsets[bin + 1];
+
+    if (LIFT) {
+        if (tid == 0) {
+            s_ctx.cam = load_cam(viewmats + cam * 16, Ks + cam * 9);
+            s_ctx.means = means; s_ctx.quats = quats; s_ctx.scales = scales;
+            s_ctx.W = W; s_ctx.H = H; s_ctx.N = N; s_ctx.cam_index = cam; s_ctx.eps2d = eps2d;
+        }
+        for (int q = tid; q < 12 * BWD_BATCH; q += 256) s_pose[q] = 0.f;
+    }
 
     const float T_final = inside ? 1.f - render_alphas[pix] : 1.f;
     float T = T_final;
@@ -124,7 +169,8 @@ __global__ void __launch_bounds__(256) raster_bwd_kernel(
 #pragma unroll
         for (int k = 0; k < CDIM; ++k) v_ra -= backgrounds[cam * CDIM + k] * v_rc[k];
     }
-    const int bin_final = inside ? last_ids[pix] : 0;
+    const float v_ra_T = T_final * v_ra;
+    const int bin_final = inside ? last_ids[pix] : -1;
     int warp_bin_final = bin_final;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) warp_bin_final = max(warp_bin_final, __shfl_xor_sync(0xffffffffu, warp_bin_final, o));
@@ -134,13 +180,12 @@ __global__ void __launch_bounds__(256) raster_bwd_kernel(
 #pragma unroll
     for (int w = 1; w < 8; ++w) block_bin_final = max(block_bin_final, s_max[w]);
 
-    Cam camera;
-    float pose_acc[12];
-    if (LIFT) {
-        camera = load_cam(viewmats + cam * 16, Ks + cam * 9);
-#pragma unroll
-        for (int k = 0; k < 12; ++k) pose_acc[k] = 0.f;
-    }
+    // which of the reduced values this lane ends up holding (see warp_reduce_multi) and where it stores it
+    const int ridx = (NV == 8) ? ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1)
+                               : ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+    const bool holder = (NV == 8) ? ((lane & 3) == 0) : ((lane & 1) == 0);
+    float* const acc_slot = s_acc + (LIFT ? wid * BWD_BATCH * 6 + ridx : 0);
+    const bool acc_writer = holder && ridx < 6;
 
     // positions > block_bin_final were composited by no pixel of this tile: start the replay there
     const int first = min(range_end - 1, block_bin_final);
@@ -150,23 +195,30 @@ __global__ void __launch_bounds__(256) raster_bwd_kernel(
         __syncthreads();  // previous batch fully consumed
         const int batch_end = first - BWD_BATCH * b;
         const int batch_size = min(BWD_BATCH, batch_end + 1 - range_start);
-        if (tid < batch_size) {
-            const int g = flatten_ids[batch_end - tid];
-            s_id[tid] = g;
-            float* dst = sm + tid * RS;
-            if (PACKED) {
-                float4 r0 = rec[2 * (size_t)g], r1 = rec[2 * (size_t)g + 1];
-                reinterpret_cast<float4*>(dst)[0] = make_float4(r0.x, r0.y, r1.x, r1.y);
-                reinterpret_cast<float4*>(dst)[1] = make_float4(r1.z, r0.w, r0.z, 0.f);
-            } else {
-                float2 xy = reinterpret_cast<const float2*>(means2d)[g];
-                reinterpret_cast<float4*>(dst)[0] =
-                    make_float4(xy.x, xy.y, conics[3 * (size_t)g], conics[3 * (size_t)g + 1]);
-                dst[4] = conics[3 * (size_t)g + 2];
-                dst[5] = opacities[g];
+        if (tid < BWD_BATCH) {
+            unsigned m = 0u;
+            if (tid < batch_size) {
+                const int g = flatten_ids[batch_end - tid];
+                s_id[tid] = g;
+                float* dst = sm + tid * RS;
+                if (PACKED) {
+                    const float4 r0 = __ldg(rec + 2 * (size_t)g), r1 = __ldg(rec + 2 * (size_t)g + 1);
+                    reinterpret_cast<float4*>(dst)[0] = make_float4(r0.x, r0.y, r1.x, r1.y);
+                    reinterpret_cast<float4*>(dst)[1] = make_float4(r1.z, r0.w, r0.z, 0.f);
+                    m = patch_mask(r0.x, r0.y, r1.x, r1.y, r1.z, r0.w, tile_x0, tile_y0);
+                } else {
+                    const float2 xy = reinterpret_cast<const float2*>(means2d)[g];
+                    const float ca = conics[3 * (size_t)g], cb = conics[3 * (size_t)g + 1], cc = conics[3 * (size_t)g + 2];
+                    const float o = opacities[g];
+                    reinterpret_cast<float4*>(dst)[0] = make_float4(xy.x, xy.y, ca, cb);
+                    dst[4] = cc;
+                    dst[5] = o;
 #pragma unroll
-                for (int k = 0; k < CDIM; ++k) dst[6 + k] = colors[(size_t)g * CDIM + k];
+                    for (int k = 0; k < CDIM; ++k) dst[6 + k] = colors[(size_t)g * CDIM + k];
+                    m = patch_mask(xy.x, xy.y, ca, cb, cc, o, tile_x0, tile_y0);
+                }
             }
+            s_mask[tid] = (unsigned char)m;
         }
         if (LIFT) {
             float4* z = reinterpret_cast<float4*>(s_acc);
@@ -174,74 +226,64 @@ __global__ void __launch_bounds__(256) raster_bwd_kernel(
         }
         __syncthreads();
 
-        for (int t = max(0, batch_end - warp_bin_final); t < batch_size; ++t) {
-            bool valid = inside && (batch_end - t <= bin_final);
-            float alpha = 0.f, opac = 0.f, vis = 0.f, dx = 0.f, dy = 0.f;
-            const float4 p0 = reinterpret_cast<const float4*>(sm + t * RS)[0];
-            const float4 p1 = reinterpret_cast<const float4*>(sm + t * RS)[1];
-            if (valid) {
-                opac = p1.y;
-                dx = p0.x - px; dy = p0.y - py;
+        const int t_begin = max(0, batch_end - warp_bin_final);
+        const int my_first = batch_end - bin_final;   // this pixel takes part for t >= my_first (never when outside)
+        for (int c0 = t_begin & ~31; c0 < batch_size; c0 += 32) {
+            unsigned bits = __ballot_sync(0xffffffffu, ((unsigned)s_mask[c0 + lane] >> wid) & 1u);
+            if (c0 < t_begin) bits &= 0xffffffffu << (t_begin - c0);
+            while (bits) {
+                const int t = c0 + __ffs(bits) - 1;
+                bits &= bits - 1;
+                const float4 p0 = reinterpret_cast<const float4*>(sm + t * RS)[0];
+                const float4 p1 = reinterpret_cast<const float4*>(sm + t * RS)[1];
+                const float opac = p1.y;
+                const float dx = p0.x - px, dy = p0.y - py;
                 const float sigma = 0.5f * (p0.z * dx * dx + p1.x * dy * dy) + p0.w * dx * dy;
-                vis = __expf(-sigma);
-                alpha = fminf(GSB_ALPHA_MAX, opac * vis);
-                if (sigma < 0.f || alpha < GSB_ALPHA_MIN) valid = false;
-            }
-            if (!__any_sync(0xffffffffu, valid)) continue;
-            // v[]: 0,1 = v_xy; 2,3,4 = v_conic; 5 = v_opacity (generic) ; 6.. = v_colour
-            //      LIFT: 5 = v_colour (depth) and v_opacity is not needed
-            float v[NV];
+                const float vis = exp_neg_fast(sigma);
+                const float alpha = fminf(GSB_ALPHA_MAX, opac * vis);
+                const bool valid = inside && (t >= my_first) && !(sigma < 0.f || alpha < GSB_ALPHA_MIN);
+                if (!__any_sync(0xffffffffu, valid)) continue;
+                // v[]: 0,1 = v_xy; 2,3,4 = v_conic; 5 = v_opacity (generic) ; 6.. = v_colour
+                //      LIFT: 5 = v_colour (depth) and v_opacity is not needed
+                float v[NV];
 #pragma unroll
-            for (int k = 0; k < NV; ++k) v[k] = 0.f;
-            if (valid) {
-                const float ra = 1.f / (1.f - alpha);
-                T *= ra;
-                const float fac = alpha * T;
-                float col[CDIM];
-                col[0] = p1.z;
-                if (CDIM > 1) col[1 < CDIM ? 1 : 0] = p1.w;
+                for (int k = 0; k < NV; ++k) v[k] = 0.f;
+                if (valid) {
+                    const float ra = rcp_fast(1.f - alpha);   // 1 - alpha >= 1e-3
+                    T *= ra;
+                    const float fac = alpha * T;
+                    float col[CDIM];
+                    col[0] = p1.z;
+                    if (CDIM > 1) col[1 < CDIM ? 1 : 0] = p1.w;
 #pragma unroll
-                for (int k = 2; k < CDIM; ++k) col[k] = sm[t * RS + 6 + k];
-                float v_alpha = 0.f;
+                    for (int k = 2; k < CDIM; ++k) col[k] = sm[t * RS + 6 + k];
+                    float v_alpha = 0.f;
 #pragma unroll
-                for (int k = 0; k < CDIM; ++k) {
-                    v[(LIFT ? 5 : 6) + k] = fac * v_rc[k];
-                    v_alpha += (col[k] * T - buffer[k] * ra) * v_rc[k];
-                }
-                v_alpha += T_final * ra * v_ra;
-                if (opac * vis <= GSB_ALPHA_MAX) {
-                    const float v_sigma = -opac * vis * v_alpha;
-                    v[2] = 0.5f * v_sigma * dx * dx;
-                    v[3] = v_sigma * dx * dy;
-                    v[4] = 0.5f * v_sigma * dy * dy;
-                    v[0] = v_sigma * (p0.z * dx + p0.w * dy);
-                    v[1] = v_sigma * (p0.w * dx + p1.x * dy);
-                    if (!LIFT) v[5] = vis * v_alpha;
-                }
-#pragma unroll
-                for (int k = 0; k < CDIM; ++k) buffer[k] += col[k] * fac;
-            }
-            warp_reduce_multi<NV>(v, lane);
-            if (NV == 8) {
-                const int idx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
-                if ((lane & 3) == 0) {
-                    if (LIFT) {
-                        if (idx < 6) s_acc[(wid * BWD_BATCH + t) * 6 + idx] = v[0];
-                    } else if (idx < 6 + CDIM) {
-                        const size_t g = (size_t)s_id[t];
-                        float* dst = idx < 2 ? v_means2d + 2 * g + idx
-                                   : idx < 5 ? v_conics + 3 * g + (idx - 2)
-                                   : idx == 5 ? v_opacities + g : v_colors + g * CDIM + (idx - 6);
-                        atomicAdd(dst, v[0]);
+                    for (int k = 0; k < CDIM; ++k) {
+                        v[(LIFT ? 5 : 6) + k] = fac * v_rc[k];
+                        v_alpha += (col[k] * T - buffer[k] * ra) * v_rc[k];
                     }
+                    v_alpha += v_ra_T * ra;
+                    if (opac * vis <= GSB_ALPHA_MAX) {
+                        const float v_sigma = -opac * vis * v_alpha;
+                        v[2] = 0.5f * v_sigma * dx * dx;
+                        v[3] = v_sigma * dx * dy;
+                        v[4] = 0.5f * v_sigma * dy * dy;
+                        v[0] = v_sigma * (p0.z * dx + p0.w * dy);
+                        v[1] = v_sigma * (p0.w * dx + p1.x * dy);
+                        if (!LIFT) v[5] = vis * v_alpha;
+                    }
+#pragma unroll
+                    for (int k = 0; k < CDIM; ++k) buffer[k] += col[k] * fac;
                 }
-            } else {
-                const int idx = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
-                if ((lane & 1) == 0 && idx < 6 + CDIM) {
+                warp_reduce_multi<NV>(v, lane);
+                if (LIFT) {
+                    if (acc_writer) acc_slot[t * 6] = v[0];
+                } else if (holder && ridx < 6 + CDIM) {
                     const size_t g = (size_t)s_id[t];
-                    float* dst = idx < 2 ? v_means2d + 2 * g + idx
-                               : idx < 5 ? v_conics + 3 * g + (idx - 2)
-                               : idx == 5 ? v_opacities + g : v_colors + g * CDIM + (idx - 6);
+                    float* dst = ridx < 2 ? v_means2d + 2 * g + ridx
+                               : ridx < 5 ? v_conics + 3 * g + (ridx - 2)
+                               : ridx == 5 ? v_opacities + g : v_colors + g * CDIM + (ridx - 6);
                     atomicAdd(dst, v[0]);
                 }
             }
@@ -262,35 +304,20 @@ __global__ void __launch_bounds__(256) raster_bwd_kernel(
                 bool any = false;
 #pragma unroll
                 for (int k = 0; k < 6; ++k) any |= (gsum[k] != 0.f);
-                if (any) {
-                    const int n = s_id[tid] - cam * N;
-                    float mean[3] = {means[n * 3], means[n * 3 + 1], means[n * 3 + 2]};
-                    float4 q4 = reinterpret_cast<const float4*>(quats)[n];
-                    float q[4] = {q4.x, q4.y, q4.z, q4.w};
-                    float s[3] = {scales[n * 3], scales[n * 3 + 1], scales[n * 3 + 2]};
-                    Proj p; float S[6], Sc[6];
-                    project_gaussian(camera, mean, q, s, W, H, eps2d, -1e30f, 1e30f, -1.f, p, S, Sc);
-                    float v_pc[3], vS[6];
-                    project_vjp(camera, p, Sc, gsum[0], gsum[1], gsum[2], gsum[3], gsum[4], gsum[5], v_pc, vS);
-                    pose_accumulate(camera, mean, S, v_pc, vS, pose_acc, pose_acc + 9);
-                }
+                if (any) lift_to_pose(&s_ctx, s_id[tid], gsum[0], gsum[1], gsum[2], gsum[3], gsum[4], gsum[5], s_pose + tid);
             }
         }
     }
 
     if (LIFT) {
         __syncthreads();
-#pragma unroll
-        for (int k = 0; k < 12; ++k) {
-            float s = warp_sum(pose_acc[k]);
-            if (lane == 0) s_red[k * 8 + wid] = s;
-        }
-        __syncthreads();
-        if (tid < 12) {
+        // 12 numbers x BWD_BATCH thread columns -> one 12-float partial of this tile (fixed order: deterministic)
+        for (int k = wid; k < 12; k += 8) {
             float s = 0.f;
 #pragma unroll
-            for (int w = 0; w < 8; ++w) s += s_red[tid * 8 + w];
-            partials[(size_t)bin * 12 + tid] = s;
+            for (int q = 0; q < BWD_BATCH / 32; ++q) s += s_pose[k * BWD_BATCH + q * 32 + lane];
+            s = warp_sum(s);
+            if (lane == 0) partials[(size_t)bin * 12 + k] = s;
         }
     }
 }

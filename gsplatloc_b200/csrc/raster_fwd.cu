@@ -1,6 +1,9 @@
 // Per-tile front-to-back compositing (Appendix A.4).
-// One 256-thread block per (camera, 16x16 tile); sorted Gaussians are gathered in batches of 256 into shared
-// memory as 32/48-byte records and broadcast-read by all pixels of the tile.
+// One 256-thread block per (camera, 16x16 tile); each warp owns an 8x4 pixel patch.  Sorted Gaussians are gathered
+// in batches of 256 into shared memory as 32/48-byte records together with an 8-bit patch mask (common.cuh:
+// which warps' patches the alpha >= 1/255 ellipse can reach).  A warp ballots its bit over 32 records at a time and
+// walks only the set bits, so a record that cannot touch the patch costs ~1/32 of a ballot instead of a full
+// per-pixel alpha evaluation; the per-pixel test itself is unchanged (results are identical to walking the list).
 //   PACKED = true : tracker path. Gaussians come as the two-sector record written by project_bin_kernel and the
 //                   single colour channel is the depth (render_mode "D"/"ED"); the ED quotient can be fused into
 //                   the epilogue.
@@ -15,23 +18,28 @@ struct RecStride {
     static constexpr int value = (CDIM <= 2) ? 8 : ((CDIM <= 6) ? 12 : 16);  // floats per staged record
 };
 
+// dst: {x, y, a, b | c, opac, col0, col1 | col2 ...}; returns the patch mask of the Gaussian in this tile
 template <int CDIM, bool PACKED>
-__device__ __forceinline__ void stage_gaussian(float* __restrict__ dst, int g, const float4* __restrict__ rec,
-                                               const float* __restrict__ means2d, const float* __restrict__ conics,
-                                               const float* __restrict__ colors, const float* __restrict__ opac) {
-    // dst: {x, y, a, b | c, opac, col0, col1 | col2 ...}
+__device__ __forceinline__ unsigned stage_gaussian(float* __restrict__ dst, int g, const float4* __restrict__ rec,
+                                                   const float* __restrict__ means2d,
+                                                   const float* __restrict__ conics,
+                                                   const float* __restrict__ colors, const float* __restrict__ opac,
+                                                   float tile_x0, float tile_y0) {
     if (PACKED) {
-        float4 r0 = rec[2 * (size_t)g], r1 = rec[2 * (size_t)g + 1];
+        const float4 r0 = __ldg(rec + 2 * (size_t)g), r1 = __ldg(rec + 2 * (size_t)g + 1);
         reinterpret_cast<float4*>(dst)[0] = make_float4(r0.x, r0.y, r1.x, r1.y);
         reinterpret_cast<float4*>(dst)[1] = make_float4(r1.z, r0.w, r0.z, 0.f);
+        return patch_mask(r0.x, r0.y, r1.x, r1.y, r1.z, r0.w, tile_x0, tile_y0);
     } else {
-        float2 xy = reinterpret_cast<const float2*>(means2d)[g];
-        float a = conics[3 * (size_t)g], b = conics[3 * (size_t)g + 1], c = conics[3 * (size_t)g + 2];
+        const float2 xy = reinterpret_cast<const float2*>(means2d)[g];
+        const float a = conics[3 * (size_t)g], b = conics[3 * (size_t)g + 1], c = conics[3 * (size_t)g + 2];
+        const float o = opac[g];
         reinterpret_cast<float4*>(dst)[0] = make_float4(xy.x, xy.y, a, b);
         dst[4] = c;
-        dst[5] = opac[g];
+        dst[5] = o;
 #pragma unroll
         for (int k = 0; k < CDIM; ++k) dst[6 + k] = colors[(size_t)g * CDIM + k];
+        return patch_mask(xy.x, xy.y, a, b, c, o, tile_x0, tile_y0);
     }
 }
 
@@ -44,12 +52,15 @@ __global__ void __launch_bounds__(256) raster_fwd_kernel(
     float* __restrict__ render_alphas, int* __restrict__ last_ids, int normalize_last, const int* __restrict__ stop) {
     constexpr int RS = RecStride<CDIM>::value;
     __shared__ __align__(16) float sm[256 * RS];
+    __shared__ unsigned char s_mask[256];
     const int cam = blockIdx.z;
     if (stop && stop[cam]) return;
     const int tile_id = blockIdx.y * tile_w + blockIdx.x;
-    const int tid = threadIdx.y * 16 + threadIdx.x;
-    const int i = blockIdx.y * 16 + threadIdx.y, j = blockIdx.x * 16 + threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int j = blockIdx.x * 16 + (wid & 1) * 8 + (lane & 7);
+    const int i = blockIdx.y * 16 + (wid >> 1) * 4 + (lane >> 3);
     const float px = (float)j + 0.5f, py = (float)i + 0.5f;
+    const float tile_x0 = (float)(blockIdx.x * 16), tile_y0 = (float)(blockIdx.y * 16);
     const bool inside = (i < H) && (j < W);
     bool done = !inside;
     const int n_isects = n_isects_dev ? *n_isects_dev : n_isects_host;
@@ -63,34 +74,52 @@ __global__ void __launch_bounds__(256) raster_fwd_kernel(
     float out[CDIM];
 #pragma unroll
     for (int k = 0; k < CDIM; ++k) out[k] = 0.f;
+    bool warp_done = __all_sync(0xffffffffu, done);
 
     for (int b = 0; b < num_batches; ++b) {
         if (__syncthreads_count(done) >= 256) break;
         const int batch_start = range_start + 256 * b;
         const int idx = batch_start + tid;
+        unsigned m = 0u;
         if (idx < range_end)
-            stage_gaussian<CDIM, PACKED>(sm + tid * RS, flatten_ids[idx], rec, means2d, conics, colors, opacities);
+            m = stage_gaussian<CDIM, PACKED>(sm + tid * RS, flatten_ids[idx], rec, means2d, conics, colors, opacities,
+                                             tile_x0, tile_y0);
+        s_mask[tid] = (unsigned char)m;
         __syncthreads();
+        if (warp_done) continue;
         const int batch_size = min(256, range_end - batch_start);
-        for (int t = 0; (t < batch_size) && !done; ++t) {
-            const float4 p0 = reinterpret_cast<const float4*>(sm + t * RS)[0];
-            const float4 p1 = reinterpret_cast<const float4*>(sm + t * RS)[1];
-            const float dx = p0.x - px, dy = p0.y - py;
-            const float sigma = 0.5f * (p0.z * dx * dx + p1.x * dy * dy) + p0.w * dx * dy;
-            const float alpha = fminf(GSB_ALPHA_MAX, p1.y * __expf(-sigma));
-            if (sigma < 0.f || alpha < GSB_ALPHA_MIN) continue;
-            const float next_T = T * (1.f - alpha);
-            if (next_T <= GSB_T_STOP) {  // this entry is NOT composited
-                done = true;
-                break;
-            }
-            const float vis = alpha * T;
-            out[0] += p1.z * vis;
-            if (CDIM > 1) out[1 < CDIM ? 1 : 0] += p1.w * vis;
+        for (int c0 = 0; c0 < batch_size; c0 += 32) {
+            unsigned bits = __ballot_sync(0xffffffffu, ((unsigned)s_mask[c0 + lane] >> wid) & 1u);
+            while (bits) {
+                const int t = c0 + __ffs(bits) - 1;
+                bits &= bits - 1;
+                if (!done) {
+                    const float4 p0 = reinterpret_cast<const float4*>(sm + t * RS)[0];
+                    const float4 p1 = reinterpret_cast<const float4*>(sm + t * RS)[1];
+                    const float dx = p0.x - px, dy = p0.y - py;
+                    const float sigma = 0.5f * (p0.z * dx * dx + p1.x * dy * dy) + p0.w * dx * dy;
+                    const float alpha = fminf(GSB_ALPHA_MAX, p1.y * exp_neg_fast(sigma));
+                    if (!(sigma < 0.f || alpha < GSB_ALPHA_MIN)) {
+                        const float next_T = T * (1.f - alpha);
+                        if (next_T <= GSB_T_STOP) {  // this entry is NOT composited
+                            done = true;
+                        } else {
+                            const float vis = alpha * T;
+                            out[0] += p1.z * vis;
+                            if (CDIM > 1) out[1 < CDIM ? 1 : 0] += p1.w * vis;
 #pragma unroll
-            for (int k = 2; k < CDIM; ++k) out[k] += sm[t * RS + 6 + k] * vis;
-            cur_idx = batch_start + t;
-            T = next_T;
+                            for (int k = 2; k < CDIM; ++k) out[k] += sm[t * RS + 6 + k] * vis;
+                            cur_idx = batch_start + t;
+                            T = next_T;
+                        }
+                    }
+                }
+                if (__all_sync(0xffffffffu, done)) {
+                    warp_done = true;
+                    break;
+                }
+            }
+            if (warp_done) break;
         }
     }
     if (inside) {
@@ -113,8 +142,8 @@ static void launch_t(int C, int W, int H, int tile_w, int tile_h, const float4* 
                      const int* tile_offsets, const int* n_isects_dev, int n_isects_host, const int* flatten_ids,
                      float* render_colors, float* render_alphas, int* last_ids, int normalize_last, const int* stop,
                      cudaStream_t st) {
-    dim3 grid(tile_w, tile_h, C), block(16, 16, 1);
-    raster_fwd_kernel<CDIM, PACKED><<<grid, block, 0, st>>>(C, W, H, tile_w, tile_h, rec, means2d, conics, colors,
+    dim3 grid(tile_w, tile_h, C);
+    raster_fwd_kernel<CDIM, PACKED><<<grid, 256, 0, st>>>(C, W, H, tile_w, tile_h, rec, means2d, conics, colors,
                                                             opacities, backgrounds, tile_offsets, n_isects_dev,
                                                             n_isects_host, flatten_ids, render_colors, render_alphas,
                                                             last_ids, normalize_last, stop);
