@@ -111,7 +111,7 @@ __device__ __noinline__ void lift_to_pose(const LiftCtx* __restrict__ ctx, int f
 }
 
 template <int CDIM, bool PACKED, bool LIFT>
-__global__ void __launch_bounds__(256) raster_bwd_kernel(
+__global__ void __launch_bounds__(256, LIFT ? 4 : 2) raster_bwd_kernel(
     int C, int N, int W, int H, int tile_w, int tile_h, const float4* __restrict__ rec,
     const float* __restrict__ means2d, const float* __restrict__ conics, const float* __restrict__ colors,
     const float* __restrict__ opacities, const float* __restrict__ backgrounds,

@@ -93,33 +93,29 @@ __global__ void __launch_bounds__(256) raster_fwd_kernel(
             while (bits) {
                 const int t = c0 + __ffs(bits) - 1;
                 bits &= bits - 1;
-                if (!done) {
-                    const float4 p0 = reinterpret_cast<const float4*>(sm + t * RS)[0];
-                    const float4 p1 = reinterpret_cast<const float4*>(sm + t * RS)[1];
-                    const float dx = p0.x - px, dy = p0.y - py;
-                    const float sigma = 0.5f * (p0.z * dx * dx + p1.x * dy * dy) + p0.w * dx * dy;
-                    const float alpha = fminf(GSB_ALPHA_MAX, p1.y * exp_neg_fast(sigma));
-                    if (!(sigma < 0.f || alpha < GSB_ALPHA_MIN)) {
-                        const float next_T = T * (1.f - alpha);
-                        if (next_T <= GSB_T_STOP) {  // this entry is NOT composited
-                            done = true;
-                        } else {
-                            const float vis = alpha * T;
-                            out[0] += p1.z * vis;
-                            if (CDIM > 1) out[1 < CDIM ? 1 : 0] += p1.w * vis;
+                const float4 p0 = reinterpret_cast<const float4*>(sm + t * RS)[0];
+                const float4 p1 = reinterpret_cast<const float4*>(sm + t * RS)[1];
+                const float dx = p0.x - px, dy = p0.y - py;
+                const float sigma = 0.5f * (p0.z * dx * dx + p1.x * dy * dy) + p0.w * dx * dy;
+                const float alpha = fminf(GSB_ALPHA_MAX, p1.y * exp_neg_fast(sigma));
+                const float next_T = T * (1.f - alpha);
+                const bool hit = !done && !(sigma < 0.f || alpha < GSB_ALPHA_MIN);
+                const bool comp = hit && next_T > GSB_T_STOP;   // an entry that would end the pixel is NOT composited
+                done = done || (hit && !comp);
+                if (comp) {
+                    const float vis = alpha * T;
+                    out[0] += p1.z * vis;
+                    if (CDIM > 1) out[1 < CDIM ? 1 : 0] += p1.w * vis;
 #pragma unroll
-                            for (int k = 2; k < CDIM; ++k) out[k] += sm[t * RS + 6 + k] * vis;
-                            cur_idx = batch_start + t;
-                            T = next_T;
-                        }
-                    }
-                }
-                if (__all_sync(0xffffffffu, done)) {
-                    warp_done = true;
-                    break;
+                    for (int k = 2; k < CDIM; ++k) out[k] += sm[t * RS + 6 + k] * vis;
+                    cur_idx = batch_start + t;
+                    T = next_T;
                 }
             }
-            if (warp_done) break;
+            if (__all_sync(0xffffffffu, done)) {  // checked once per 32 staged records, not per record
+                warp_done = true;
+                break;
+            }
         }
     }
     if (inside) {
