@@ -23,7 +23,7 @@ class TrackerConfig(C.Structure):
     _fields_ = [("lr_quat", c_f), ("lr_trans", c_f), ("wd_quat", c_f), ("wd_trans", c_f), ("beta1", c_f),
                 ("beta2", c_f), ("adam_eps", c_f), ("lr_gamma", c_f), ("depth_lambda", c_f), ("normal_lambda", c_f),
                 ("early_stop", c_i), ("patience", c_i), ("warmup", c_i), ("eps2d", c_f), ("near_plane", c_f),
-                ("far_plane", c_f), ("radius_clip", c_f)]
+                ("far_plane", c_f), ("radius_clip", c_f), ("normal_mode", c_i)]
 
 
 class PoseState(C.Structure):
@@ -56,6 +56,9 @@ _SIGS = {
     "gsb_sh_fwd": (c_i, [c_i, c_i, c_i, c_p, c_p, c_p, c_p, c_p]),
     "gsb_sh_bwd": (c_i, [c_i, c_i, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),
     "gsb_depth_edge_loss": (c_i, [c_i, c_i, c_i, c_p, c_p, c_i, c_i, c_f, c_f, c_p, c_p, c_p, c_p]),
+    "gsb_loss_workspace_floats": (c_sz, [c_i, c_i, c_i]),
+    "gsb_depth_edge_normal_loss": (c_i, [c_i, c_i, c_i, c_p, c_p, c_i, c_i, c_p, c_f, c_f, c_f, c_i, c_p, c_p, c_p,
+                                         c_p]),
     "gsb_tracker_default_config": (None, [C.POINTER(TrackerConfig), c_i]),
     "gsb_tracker_create": (c_i, [C.POINTER(c_p), c_i, c_i, c_i, c_p]),
     "gsb_tracker_destroy": (None, [c_p]),

@@ -18,21 +18,24 @@ int fail(int code, const char* what, cudaError_t e) {
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 static inline int tile_bits_of(int n_tiles) { return (int)floor(log2((double)n_tiles)) + 1; }
 
-__global__ void reduce_loss_partials_kernel(int nblk, const float* __restrict__ partial, float* __restrict__ sums) {
-    __shared__ float red[2][8];
+// partial: 3 floats per loss block; sums: the first ``nout`` of them per camera
+__global__ void reduce_loss_partials_kernel(int nblk, const float* __restrict__ partial, float* __restrict__ sums,
+                                            int nout) {
+    __shared__ float red[3][8];
     int c = blockIdx.x, tid = threadIdx.x;
-    float a = 0.f, b = 0.f;
+    float a = 0.f, b = 0.f, d = 0.f;
     for (int i = tid; i < nblk; i += 256) {
-        a += partial[((size_t)c * nblk + i) * 2];
-        b += partial[((size_t)c * nblk + i) * 2 + 1];
+        a += partial[((size_t)c * nblk + i) * 3];
+        b += partial[((size_t)c * nblk + i) * 3 + 1];
+        d += partial[((size_t)c * nblk + i) * 3 + 2];
     }
-    a = warp_sum(a); b = warp_sum(b);
-    if ((tid & 31) == 0) { red[0][tid >> 5] = a; red[1][tid >> 5] = b; }
+    a = warp_sum(a); b = warp_sum(b); d = warp_sum(d);
+    if ((tid & 31) == 0) { red[0][tid >> 5] = a; red[1][tid >> 5] = b; red[2][tid >> 5] = d; }
     __syncthreads();
-    if (tid < 2) {
+    if (tid < nout) {
         float s = 0.f;
         for (int w = 0; w < 8; ++w) s += red[tid][w];
-        sums[c * 2 + tid] = s;
+        sums[c * nout + tid] = s;
     }
 }
 }  // namespace gsb
@@ -208,9 +211,33 @@ int gsb_depth_edge_loss(int C, int width, int height, const float* depth, const 
     int gx, gy;
     loss_grid(width, height, &gx, &gy);
     launch_loss(C, width, height, depth, nullptr, gt, gt_per_camera ? (size_t)width * height : 0, apply_mask, w_d,
-                w_s, 0, v_depth, nullptr, partial_ws, nullptr, st);
-    reduce_loss_partials_kernel<<<C, 256, 0, st>>>(gx * gy, partial_ws, loss_sums);
+                w_s, 0.f, 0, nullptr, nullptr, 0, v_depth, nullptr, partial_ws, nullptr, st);
+    reduce_loss_partials_kernel<<<C, 256, 0, st>>>(gx * gy, partial_ws, loss_sums, 2);
     CK_LAUNCH("gsb_depth_edge_loss");
+    return GSB_OK;
+}
+
+size_t gsb_loss_workspace_floats(int C, int width, int height) {
+    int gx, gy;
+    loss_grid(width, height, &gx, &gy);
+    return (size_t)3 * C * gx * gy + (size_t)9 * C * height;
+}
+
+int gsb_depth_edge_normal_loss(int C, int width, int height, const float* depth, const float* gt, int gt_per_camera,
+                               int apply_mask, const float* Ks, float w_d, float w_s, float lambda_n,
+                               int normal_mode, float* loss_sums, float* v_depth, float* ws, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (C <= 0 || width <= 0 || height <= 0) return fail(GSB_ERR_ARG, "gsb_depth_edge_normal_loss: bad sizes", cudaSuccess);
+    if (normal_mode < 0 || normal_mode > 2) return fail(GSB_ERR_ARG, "gsb_depth_edge_normal_loss: normal_mode must be 0, 1 or 2", cudaSuccess);
+    if (normal_mode != 0 && !Ks) return fail(GSB_ERR_ARG, "gsb_depth_edge_normal_loss: Ks is required for the normal term", cudaSuccess);
+    int gx, gy;
+    loss_grid(width, height, &gx, &gy);
+    float* rows = ws + (size_t)3 * C * gx * gy;
+    // lambda_n == 0 switches the term off inside launch_loss; keep the cosine sum defined (0) in that case
+    launch_loss(C, width, height, depth, nullptr, gt, gt_per_camera ? (size_t)width * height : 0, apply_mask, w_d,
+                w_s, lambda_n, normal_mode, Ks, rows, 0, v_depth, nullptr, ws, nullptr, st);
+    reduce_loss_partials_kernel<<<C, 256, 0, st>>>(gx * gy, ws, loss_sums, 3);
+    CK_LAUNCH("gsb_depth_edge_normal_loss");
     return GSB_OK;
 }
 

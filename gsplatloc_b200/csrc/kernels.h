@@ -70,14 +70,15 @@ int launch_raster_bwd_soa(int cdim, int C, int N, int W, int H, int tile_w, int 
 // ---- loss.cu
 void loss_grid(int W, int H, int* gx, int* gy);
 void launch_loss(int C, int W, int H, const float* ed, const float* alpha, const float* gt, size_t gt_cam_stride,
-                 int apply_mask, float w_d, float w_s, int mode, float* v_out, float* v_alpha, float* partial,
-                 const int* stop, cudaStream_t st);
+                 int apply_mask, float w_d, float w_s, float lambda_n, int normal_mode, const float* Ks,
+                 float* normal_rows, int mode, float* v_out, float* v_alpha, float* partial, const int* stop,
+                 cudaStream_t st);
 
 // ---- pose.cu
 void launch_pose_begin(int C, const gsb_pose_state* state, float* viewmats, cudaStream_t st);
 void launch_pose_finish(int C, int n_tiles, int n_loss_blocks, const float* partials, const float* loss_partials,
                         const float* viewmats, gsb_pose_state* state, int* stop, gsb_tracker_config cfg,
-                        float inv_pixels, float* history, int history_cap, cudaStream_t st);
+                        float inv_pixels, float inv_rows3, float* history, int history_cap, cudaStream_t st);
 
 // ---- sh.cu
 void launch_sh_fwd(int n, int K, int degree, const float* dirs, const float* coeffs, const uint8_t* masks,

@@ -19,20 +19,105 @@ namespace gsb {
 
 __device__ __forceinline__ float sgn(float x) { return (float)((x > 0.f) - (x < 0.f)); }
 
+// ---- normal-consistency term (loss.py:62-101, geometry.py:138-197) ----------------------
+// n(D) at pixel (x, y): P = D * ((u-cx)/fx, (v-cy)/fy, 1) (kornia depth_to_3d_v2), replicate padding,
+// dx = P[y][x+1] - P[y][x-1], dy = P[y+1][x] - P[y-1][x], n = cross(dx, dy) / max(|cross|, 1e-12) (F.normalize).
+struct Normal {
+    float dx[3], dy[3];  // central differences of the back-projected points
+    float n[3];          // unit normal (or 0)
+    float len;           // |cross(dx, dy)|
+};
+
+__device__ __forceinline__ void normal_from_depths(float Dl, float Dr, float Du, float Dd, float rxm, float rxp,
+                                                   float rx, float rym, float ryp, float ry, Normal& o) {
+    const float dz_x = Dr - Dl, dz_y = Dd - Du;
+    o.dx[0] = Dr * rxp - Dl * rxm; o.dx[1] = dz_x * ry; o.dx[2] = dz_x;
+    o.dy[0] = dz_y * rx; o.dy[1] = Dd * ryp - Du * rym; o.dy[2] = dz_y;
+    const float c0 = o.dx[1] * o.dy[2] - o.dx[2] * o.dy[1];
+    const float c1 = o.dx[2] * o.dy[0] - o.dx[0] * o.dy[2];
+    const float c2 = o.dx[0] * o.dy[1] - o.dx[1] * o.dy[0];
+    o.len = sqrtf(c0 * c0 + c1 * c1 + c2 * c2);
+    const float inv = 1.f / fmaxf(o.len, 1e-12f);
+    o.n[0] = c0 * inv; o.n[1] = c1 * inv; o.n[2] = c2 * inv;
+}
+
+// Reference-faithful reduction (loss.py:93, cosine_similarity over dim=1 == image width):
+// per (row, channel) sums {sum nB*nA, sum nA^2, sum nB^2} -> rows[(cam*H + y)*9 + {0..2, 3..5, 6..8}].
+__global__ void __launch_bounds__(256) normal_rowsum_kernel(int W, int H, const float* __restrict__ ed,
+                                                            const float* __restrict__ gt, size_t gt_cam_stride,
+                                                            int apply_mask, const float* __restrict__ Ks,
+                                                            float* __restrict__ rows, const int* __restrict__ stop) {
+    __shared__ float red[9][8];
+    const int y = blockIdx.x, cam = blockIdx.y, tid = threadIdx.x;
+    if (stop && stop[cam]) return;
+    const float* d_img = ed + (size_t)cam * H * W;
+    const float* g_img = gt + (size_t)cam * gt_cam_stride;
+    const float* K = Ks + cam * 9;
+    const float ifx = 1.f / K[0], ify = 1.f / K[4], cx = K[2], cy = K[5];
+    const int ym = max(y - 1, 0), yp = min(y + 1, H - 1);
+    const float ry = ((float)y - cy) * ify, rym = ((float)ym - cy) * ify, ryp = ((float)yp - cy) * ify;
+    float acc[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) acc[k] = 0.f;
+    for (int x = tid; x < W; x += 256) {
+        const int xm = max(x - 1, 0), xp = min(x + 1, W - 1);
+        const float rx = ((float)x - cx) * ifx, rxm = ((float)xm - cx) * ifx, rxp = ((float)xp - cx) * ifx;
+        const float Al = d_img[(size_t)y * W + xm], Ar = d_img[(size_t)y * W + xp];
+        const float Au = d_img[(size_t)ym * W + x], Ad = d_img[(size_t)yp * W + x];
+        float Bl = g_img[(size_t)y * W + xm], Br = g_img[(size_t)y * W + xp];
+        float Bu = g_img[(size_t)ym * W + x], Bd = g_img[(size_t)yp * W + x];
+        if (apply_mask) {
+            Bl = (Al != 0.f) ? Bl : 0.f; Br = (Ar != 0.f) ? Br : 0.f;
+            Bu = (Au != 0.f) ? Bu : 0.f; Bd = (Ad != 0.f) ? Bd : 0.f;
+        }
+        Normal nA, nB;
+        normal_from_depths(Al, Ar, Au, Ad, rxm, rxp, rx, rym, ryp, ry, nA);
+        normal_from_depths(Bl, Br, Bu, Bd, rxm, rxp, rx, rym, ryp, ry, nB);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            acc[k] += nB.n[k] * nA.n[k];
+            acc[3 + k] += nA.n[k] * nA.n[k];
+            acc[6 + k] += nB.n[k] * nB.n[k];
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+        const float s = warp_sum(acc[k]);
+        if ((tid & 31) == 0) red[k][tid >> 5] = s;
+    }
+    __syncthreads();
+    if (tid < 9) {
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) s += red[tid][w];
+        rows[((size_t)cam * H + y) * 9 + tid] = s;
+    }
+}
+
+// NMODE: 0 = no normal term, 1 = per-pixel cosine (dim=-1), 2 = reference-faithful cosine over the image width
+// (dim=1; needs the row sums of normal_rowsum_kernel).  w_n = lambda_n / (H*W) (mode 1) or lambda_n / (3*H) (mode 2).
+// Block partials: {sum|A-B|, sum|E(A)-E(B)|, sum cos} (3 floats per block).
+template <int NMODE>
 __global__ void __launch_bounds__(LBX* LBY) loss_kernel(
     int C, int W, int H, const float* __restrict__ ed, const float* __restrict__ alpha,
-    const float* __restrict__ gt, size_t gt_cam_stride, int apply_mask, float w_d, float w_s, int mode,
-    float* __restrict__ v_out, float* __restrict__ v_alpha, float* __restrict__ partial,
-    const int* __restrict__ stop) {
+    const float* __restrict__ gt, size_t gt_cam_stride, int apply_mask, float w_d, float w_s, float w_n,
+    const float* __restrict__ Ks, const float* __restrict__ rows, int mode, float* __restrict__ v_out,
+    float* __restrict__ v_alpha, float* __restrict__ partial, const int* __restrict__ stop) {
     __shared__ float sA[LH][LW], sB[LH][LW];
     __shared__ float sKx[LBY + 2][LBX + 2], sKy[LBY + 2][LBX + 2];
-    __shared__ float s_red[2][8];
+    __shared__ float sHn[NMODE ? 6 : 1][LBY + 2][LBX + 2];   // Hx = dy x G, Hy = G x dx of the halo-1 window
+    __shared__ float s_red[3][8];
     const int cam = blockIdx.z;
     if (stop && stop[cam]) return;
     const int tid = threadIdx.y * LBX + threadIdx.x;
     const int x0 = blockIdx.x * LBX, y0 = blockIdx.y * LBY;
     const float* d_img = ed + (size_t)cam * H * W;
     const float* g_img = gt + (size_t)cam * gt_cam_stride;
+    float ifx = 0.f, ify = 0.f, cx = 0.f, cy = 0.f;
+    if (NMODE) {
+        const float* K = Ks + cam * 9;
+        ifx = 1.f / K[0]; ify = 1.f / K[4]; cx = K[2]; cy = K[5];
+    }
 
     for (int q = tid; q < LH * LW; q += LBX * LBY) {
         int r = q / LW, c = q % LW;
@@ -44,14 +129,16 @@ __global__ void __launch_bounds__(LBX* LBY) loss_kernel(
     }
     __syncthreads();
 
-    float sum_d = 0.f, sum_s = 0.f;
+    float sum_d = 0.f, sum_s = 0.f, sum_n = 0.f;
     for (int q = tid; q < (LBY + 2) * (LBX + 2); q += LBX * LBY) {
         int r = q / (LBX + 2), c = q % (LBX + 2);
         int y = y0 + r - 1, x = x0 + c - 1;
         float kx = 0.f, ky = 0.f;
+        float hn[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         if (y >= 0 && y < H && x >= 0 && x < W) {
             // window centre in smem coordinates
             int sr = r + 1, sc = c + 1;
+            const bool own = (r >= 1 && r <= LBY && c >= 1 && c <= LBX);  // this block's own pixel
             float a00 = sA[sr - 1][sc - 1], a01 = sA[sr - 1][sc], a02 = sA[sr - 1][sc + 1];
             float a10 = sA[sr][sc - 1], a12 = sA[sr][sc + 1];
             float a20 = sA[sr + 1][sc - 1], a21 = sA[sr + 1][sc], a22 = sA[sr + 1][sc + 1];
@@ -66,12 +153,67 @@ __global__ void __launch_bounds__(LBX* LBY) loss_kernel(
             float EB = sqrtf(gxB * gxB + gyB * gyB + 1e-6f);
             float k = w_s * sgn(EA - EB) / EA;
             kx = k * gxA; ky = k * gyA;
-            if (r >= 1 && r <= LBY && c >= 1 && c <= LBX) {  // this block's own pixel
+            if (own) {
                 sum_s += fabsf(EA - EB);
                 sum_d += fabsf(sA[sr][sc] - sB[sr][sc]);
             }
+            if (NMODE) {
+                const int xm = max(x - 1, 0), xp = min(x + 1, W - 1), ym = max(y - 1, 0), yp = min(y + 1, H - 1);
+                const float rx = ((float)x - cx) * ifx, rxm = ((float)xm - cx) * ifx, rxp = ((float)xp - cx) * ifx;
+                const float ry = ((float)y - cy) * ify, rym = ((float)ym - cy) * ify, ryp = ((float)yp - cy) * ify;
+                Normal nA, nB;
+                normal_from_depths(a10, a12, a01, a21, rxm, rxp, rx, rym, ryp, ry, nA);
+                normal_from_depths(b10, b12, b01, b21, rxm, rxp, rx, rym, ryp, ry, nB);
+                float gn[3];   // d(loss)/d(nA)
+                if (NMODE == 1) {
+                    const float la = sqrtf(nA.n[0] * nA.n[0] + nA.n[1] * nA.n[1] + nA.n[2] * nA.n[2]);
+                    const float lb = sqrtf(nB.n[0] * nB.n[0] + nB.n[1] * nB.n[1] + nB.n[2] * nB.n[2]);
+                    const float ia = 1.f / fmaxf(la, 1e-8f), ib = 1.f / fmaxf(lb, 1e-8f);
+                    const float cosv = (nA.n[0] * nB.n[0] + nA.n[1] * nB.n[1] + nA.n[2] * nB.n[2]) * ia * ib;
+                    if (own) sum_n += cosv;
+#pragma unroll
+                    for (int k3 = 0; k3 < 3; ++k3) gn[k3] = -w_n * (nB.n[k3] * ia * ib - cosv * nA.n[k3] * ia * ia);
+                } else {
+                    const float* rs = rows + ((size_t)cam * H + y) * 9;
+#pragma unroll
+                    for (int k3 = 0; k3 < 3; ++k3) {
+                        const float ia = 1.f / fmaxf(sqrtf(rs[3 + k3]), 1e-8f), ib = 1.f / fmaxf(sqrtf(rs[6 + k3]), 1e-8f);
+                        const float cosv = rs[k3] * ia * ib;
+                        gn[k3] = -w_n * (nB.n[k3] * ia * ib - cosv * nA.n[k3] * ia * ia);
+                    }
+                }
+                // through F.normalize: n = c / max(|c|, 1e-12)
+                float G[3];
+                if (nA.len > 1e-12f) {
+                    const float dotv = gn[0] * nA.n[0] + gn[1] * nA.n[1] + gn[2] * nA.n[2];
+                    const float il = 1.f / nA.len;
+#pragma unroll
+                    for (int k3 = 0; k3 < 3; ++k3) G[k3] = (gn[k3] - dotv * nA.n[k3]) * il;
+                } else {
+#pragma unroll
+                    for (int k3 = 0; k3 < 3; ++k3) G[k3] = gn[k3] * 1e12f;
+                }
+                // c = dx x dy:  d/d(dx) = dy x G,  d/d(dy) = G x dx
+                hn[0] = nA.dy[1] * G[2] - nA.dy[2] * G[1];
+                hn[1] = nA.dy[2] * G[0] - nA.dy[0] * G[2];
+                hn[2] = nA.dy[0] * G[1] - nA.dy[1] * G[0];
+                hn[3] = G[1] * nA.dx[2] - G[2] * nA.dx[1];
+                hn[4] = G[2] * nA.dx[0] - G[0] * nA.dx[2];
+                hn[5] = G[0] * nA.dx[1] - G[1] * nA.dx[0];
+            }
         }
         sKx[r][c] = kx; sKy[r][c] = ky;
+        if (NMODE) {
+#pragma unroll
+            for (int k3 = 0; k3 < 6; ++k3) sHn[k3][r][c] = hn[k3];
+        }
+    }
+    if (NMODE == 2 && blockIdx.x == 0 && tid < LBY * 3) {   // this block's rows: sum of the per-(row, channel) cosines
+        const int y = y0 + tid / 3, k3 = tid % 3;
+        if (y < H) {
+            const float* rs = rows + ((size_t)cam * H + y) * 9;
+            sum_n += rs[k3] / (fmaxf(sqrtf(rs[3 + k3]), 1e-8f) * fmaxf(sqrtf(rs[6 + k3]), 1e-8f));
+        }
     }
     __syncthreads();
 
@@ -107,6 +249,21 @@ __global__ void __launch_bounds__(LBX* LBY) loss_kernel(
                         }
                 }
         }
+        if (NMODE) {
+            // P[q] is the +x neighbour of (y, x-1), the -x neighbour of (y, x+1) (out-of-image entries hold 0) and,
+            // on a border, its own replicate-padded neighbour; likewise along y.
+            float gp[3];
+#pragma unroll
+            for (int k3 = 0; k3 < 3; ++k3) {
+                float g = sHn[k3][kr][kc - 1] - sHn[k3][kr][kc + 1] + sHn[3 + k3][kr - 1][kc] - sHn[3 + k3][kr + 1][kc];
+                if (x == 0) g -= sHn[k3][kr][kc];
+                if (x == W - 1) g += sHn[k3][kr][kc];
+                if (y == 0) g -= sHn[3 + k3][kr][kc];
+                if (y == H - 1) g += sHn[3 + k3][kr][kc];
+                gp[k3] = g;
+            }
+            v += gp[0] * ((float)x - cx) * ifx + gp[1] * ((float)y - cy) * ify + gp[2];
+        }
         if (apply_mask && a == 0.f) v = 0.f;
         const size_t pix = ((size_t)cam * H + y) * W + x;
         if (mode == 0) {
@@ -120,15 +277,15 @@ __global__ void __launch_bounds__(LBX* LBY) loss_kernel(
     }
 
     // block partial sums (fixed order)
-    float sd = warp_sum(sum_d), ss = warp_sum(sum_s);
-    if ((tid & 31) == 0) { s_red[0][tid >> 5] = sd; s_red[1][tid >> 5] = ss; }
+    float sd = warp_sum(sum_d), ss = warp_sum(sum_s), sn = warp_sum(sum_n);
+    if ((tid & 31) == 0) { s_red[0][tid >> 5] = sd; s_red[1][tid >> 5] = ss; s_red[2][tid >> 5] = sn; }
     __syncthreads();
-    if (tid < 2) {
+    if (tid < 3) {
         float s = 0.f;
 #pragma unroll
         for (int w = 0; w < (LBX * LBY) / 32; ++w) s += s_red[tid][w];
         size_t blk = ((size_t)cam * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
-        partial[blk * 2 + tid] = s;
+        partial[blk * 3 + tid] = s;
     }
 }
 
@@ -137,15 +294,30 @@ void loss_grid(int W, int H, int* gx, int* gy) {
     *gy = (H + LBY - 1) / LBY;
 }
 
+// normal_mode 0/1/2 as NMODE above; lambda_n is the plain weight (the 1/(H*W) or 1/(3H) is applied here); Ks[C,9]
+// and normal_rows (C*H*9 floats of scratch) are only read when normal_mode != 0 / == 2.
 void launch_loss(int C, int W, int H, const float* ed, const float* alpha, const float* gt, size_t gt_cam_stride,
-                 int apply_mask, float w_d, float w_s, int mode, float* v_out, float* v_alpha, float* partial,
-                 const int* stop, cudaStream_t st) {
+                 int apply_mask, float w_d, float w_s, float lambda_n, int normal_mode, const float* Ks,
+                 float* normal_rows, int mode, float* v_out, float* v_alpha, float* partial, const int* stop,
+                 cudaStream_t st) {
     if (C * W * H == 0) return;
     int gx, gy;
     loss_grid(W, H, &gx, &gy);
     dim3 grid(gx, gy, C), block(LBX, LBY);
-    loss_kernel<<<grid, block, 0, st>>>(C, W, H, ed, alpha, gt, gt_cam_stride, apply_mask, w_d, w_s, mode, v_out,
-                                        v_alpha, partial, stop);
+    if (lambda_n == 0.f) normal_mode = 0;
+    if (normal_mode == 2) {
+        normal_rowsum_kernel<<<dim3(H, C), 256, 0, st>>>(W, H, ed, gt, gt_cam_stride, apply_mask, Ks, normal_rows, stop);
+        loss_kernel<2><<<grid, block, 0, st>>>(C, W, H, ed, alpha, gt, gt_cam_stride, apply_mask, w_d, w_s,
+                                               lambda_n / (3.f * (float)H), Ks, normal_rows, mode, v_out, v_alpha,
+                                               partial, stop);
+    } else if (normal_mode == 1) {
+        loss_kernel<1><<<grid, block, 0, st>>>(C, W, H, ed, alpha, gt, gt_cam_stride, apply_mask, w_d, w_s,
+                                               lambda_n / ((float)W * (float)H), Ks, nullptr, mode, v_out, v_alpha,
+                                               partial, stop);
+    } else {
+        loss_kernel<0><<<grid, block, 0, st>>>(C, W, H, ed, alpha, gt, gt_cam_stride, apply_mask, w_d, w_s, 0.f,
+                                               nullptr, nullptr, mode, v_out, v_alpha, partial, stop);
+    }
 }
 
 }  // namespace gsb

@@ -58,16 +58,16 @@ __device__ __forceinline__ void adam_update(float* p, float* m, float* v, const 
 __global__ void __launch_bounds__(256) pose_finish_kernel(
     int C, int n_tiles, int n_loss_blocks, const float* __restrict__ partials,
     const float* __restrict__ loss_partials, const float* __restrict__ viewmats, gsb_pose_state* __restrict__ state,
-    int* __restrict__ stop, gsb_tracker_config cfg, float inv_pixels, float* __restrict__ history,
-    int history_cap) {
-    __shared__ float red[14][8];
+    int* __restrict__ stop, gsb_tracker_config cfg, float inv_pixels, float inv_rows3,
+    float* __restrict__ history, int history_cap) {
+    __shared__ float red[15][8];
     const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     gsb_pose_state& s = state[c];
     if (s.stopped) return;
     // fixed-order two-level sums: 12 pose-gradient numbers over tiles, 2 loss sums over loss blocks
-    float acc[14];
+    float acc[15];
 #pragma unroll
-    for (int k = 0; k < 14; ++k) acc[k] = 0.f;
+    for (int k = 0; k < 15; ++k) acc[k] = 0.f;
     const float* P = partials + (size_t)c * n_tiles * 12;
     for (int i = tid; i < n_tiles; i += 256) {
         const float4* p4 = reinterpret_cast<const float4*>(P + (size_t)i * 12);
@@ -76,21 +76,22 @@ __global__ void __launch_bounds__(256) pose_finish_kernel(
         acc[4] += b.x; acc[5] += b.y; acc[6] += b.z; acc[7] += b.w;
         acc[8] += d.x; acc[9] += d.y; acc[10] += d.z; acc[11] += d.w;
     }
-    const float* L = loss_partials + (size_t)c * n_loss_blocks * 2;
+    const float* L = loss_partials + (size_t)c * n_loss_blocks * 3;
     for (int i = tid; i < n_loss_blocks; i += 256) {
-        acc[12] += L[i * 2];
-        acc[13] += L[i * 2 + 1];
+        acc[12] += L[i * 3];
+        acc[13] += L[i * 3 + 1];
+        acc[14] += L[i * 3 + 2];
     }
 #pragma unroll
-    for (int k = 0; k < 14; ++k) {
+    for (int k = 0; k < 15; ++k) {
         float v = warp_sum(acc[k]);
         if (lane == 0) red[k][wid] = v;
     }
     __syncthreads();
     if (tid != 0) return;
-    float g[14];
+    float g[15];
 #pragma unroll
-    for (int k = 0; k < 14; ++k) {
+    for (int k = 0; k < 15; ++k) {
         float v = 0.f;
 #pragma unroll
         for (int w = 0; w < 8; ++w) v += red[k][w];
@@ -124,7 +125,10 @@ __global__ void __launch_bounds__(256) pose_finish_kernel(
     float dotq = gw * w + gx * x + gy * y + gz * z;
     float gq[4] = {(gw - dotq * w) / qnorm, (gx - dotq * x) / qnorm, (gy - dotq * y) / qnorm, (gz - dotq * z) / qnorm};
 
-    const float Ld = g[12] * inv_pixels, Ls = g[13] * inv_pixels, Ln = 0.f;
+    // L_n = 1 - mean(cos): over pixels (normal_mode 1) or over (row, channel) pairs (mode 2, loss.py:93)
+    const float Ld = g[12] * inv_pixels, Ls = g[13] * inv_pixels;
+    const float Ln = (cfg.normal_lambda != 0.f && cfg.normal_mode != 0)
+                         ? 1.f - g[14] * (cfg.normal_mode == 1 ? inv_pixels : inv_rows3) : 0.f;
     const float loss = cfg.depth_lambda * Ld + cfg.normal_lambda * Ln + (1.f - cfg.depth_lambda - cfg.normal_lambda) * Ls;
     float eT = 0.f, eR = 0.f;
     if (s.has_gt) {
@@ -184,9 +188,9 @@ void launch_pose_begin(int C, const gsb_pose_state* state, float* viewmats, cuda
 
 void launch_pose_finish(int C, int n_tiles, int n_loss_blocks, const float* partials, const float* loss_partials,
                         const float* viewmats, gsb_pose_state* state, int* stop, gsb_tracker_config cfg,
-                        float inv_pixels, float* history, int history_cap, cudaStream_t st) {
+                        float inv_pixels, float inv_rows3, float* history, int history_cap, cudaStream_t st) {
     pose_finish_kernel<<<C, 256, 0, st>>>(C, n_tiles, n_loss_blocks, partials, loss_partials, viewmats, state, stop,
-                                          cfg, inv_pixels, history, history_cap);
+                                          cfg, inv_pixels, inv_rows3, history, history_cap);
 }
 
 }  // namespace gsb

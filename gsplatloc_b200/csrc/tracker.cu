@@ -43,7 +43,7 @@ struct gsb_tracker {
     int64_t cap = 0;
     float *ed = nullptr, *alpha = nullptr, *v_depth = nullptr, *v_alpha = nullptr;
     int* last_ids = nullptr;
-    float *partials = nullptr, *loss_partials = nullptr;
+    float *partials = nullptr, *loss_partials = nullptr, *normal_rows = nullptr;
     int n_loss_blocks = 0;
     float* history = nullptr;
     int history_cap = 0;
@@ -56,7 +56,10 @@ struct gsb_tracker {
     int64_t last_n_isects = 0;
 };
 
-static const int kLaunchesPerIter = 9;
+static const int kStages = 9;   // profiled stages (the optional normal row-sum pass is timed inside "loss")
+static int n_launches_per_iter(const gsb_tracker* t) {
+    return kStages + ((t->cfg.normal_lambda != 0.f && t->cfg.normal_mode == GSB_NORMAL_REFERENCE) ? 1 : 0);
+}
 
 static void invalidate_graph(gsb_tracker* t) {
     if (t->exec) cudaGraphExecDestroy(t->exec);
@@ -64,7 +67,7 @@ static void invalidate_graph(gsb_tracker* t) {
     t->exec = nullptr; t->graph = nullptr; t->graph_valid = false;
 }
 
-// ``marks`` (nullable): kLaunchesPerIter + 1 events recorded around the kernels (profiling mode).
+// ``marks`` (nullable): kStages + 1 events recorded around the kernels (profiling mode).
 static void enqueue_iteration(gsb_tracker* t, bool forward_only, cudaEvent_t* marks = nullptr) {
     cudaStream_t st = t->stream;
     const gsb_tracker_config& c = t->cfg;
@@ -90,15 +93,15 @@ static void enqueue_iteration(gsb_tracker* t, bool forward_only, cudaEvent_t* ma
     if (forward_only) return;
     const float inv_p = 1.f / ((float)t->W * (float)t->H);
     launch_loss(C, t->W, t->H, t->ed, t->alpha, t->gt, 0, 1, c.depth_lambda * inv_p,
-                (1.f - c.depth_lambda - c.normal_lambda) * inv_p, 1, t->v_depth, t->v_alpha, t->loss_partials,
-                t->stop, st);
+                (1.f - c.depth_lambda - c.normal_lambda) * inv_p, c.normal_lambda, c.normal_mode, t->Ks,
+                t->normal_rows, 1, t->v_depth, t->v_alpha, t->loss_partials, t->stop, st);
     GSB_MARK();
     launch_raster_bwd_lift(C, N, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->offsets, t->n_isects, t->flatten_ids,
                            t->alpha, t->last_ids, t->v_depth, t->v_alpha, t->means, t->quats, t->scales, t->viewmats,
                            t->Ks, c.eps2d, t->partials, t->stop, st);
     GSB_MARK();
     launch_pose_finish(C, t->n_tiles, t->n_loss_blocks, t->partials, t->loss_partials, t->viewmats, t->state, t->stop,
-                       c, inv_p, t->history, t->history_cap, st);
+                       c, inv_p, 1.f / (3.f * (float)t->H), t->history, t->history_cap, st);
     GSB_MARK();
 #undef GSB_MARK
 }
@@ -160,6 +163,7 @@ void gsb_tracker_default_config(gsb_tracker_config* cfg, int max_steps) {
     cfg->depth_lambda = 0.8f; cfg->normal_lambda = 0.f;
     cfg->early_stop = 1; cfg->patience = 200; cfg->warmup = 100;
     cfg->eps2d = 0.3f; cfg->near_plane = 1e-2f; cfg->far_plane = 1e10f; cfg->radius_clip = 0.f;
+    cfg->normal_mode = GSB_NORMAL_REFERENCE;
 }
 
 int gsb_tracker_create(gsb_tracker** out, int C, int W, int H, void* stream) {
@@ -195,7 +199,8 @@ int gsb_tracker_create(gsb_tracker** out, int C, int W, int H, void* stream) {
     TCK(cudaMalloc(&t->v_alpha, sizeof(float) * P), "alloc");
     TCK(cudaMalloc(&t->last_ids, sizeof(int) * P), "alloc");
     TCK(cudaMalloc(&t->partials, sizeof(float) * nb * 12), "alloc");
-    TCK(cudaMalloc(&t->loss_partials, sizeof(float) * (size_t)C * t->n_loss_blocks * 2), "alloc");
+    TCK(cudaMalloc(&t->loss_partials, sizeof(float) * (size_t)C * t->n_loss_blocks * 3), "alloc");
+    TCK(cudaMalloc(&t->normal_rows, sizeof(float) * (size_t)C * H * 9), "alloc");
     TCK(cudaMalloc(&t->history, sizeof(float) * (size_t)t->history_cap * C * 8), "alloc");
     TCK(cudaMallocHost(&t->h_flags, sizeof(int) * (C + 2)), "alloc pinned");
     TCK(cudaMemsetAsync(t->counts, 0, sizeof(int) * nb, t->stream), "memset");
@@ -214,7 +219,8 @@ void gsb_tracker_destroy(gsb_tracker* t) {
     invalidate_graph(t);
     void* bufs[] = {t->means, t->quats, t->scales, t->opac, t->gt, t->Ks, t->viewmats, t->state, t->stop, t->rec,
                     t->bbox, t->counts, t->offsets, t->cursor, t->n_isects, t->keys, t->flatten_ids, t->ed, t->alpha,
-                    t->v_depth, t->v_alpha, t->last_ids, t->partials, t->loss_partials, t->history};
+                    t->v_depth, t->v_alpha, t->last_ids, t->partials, t->loss_partials, t->normal_rows,
+                    t->history};
     for (void* b : bufs)
         if (b) cudaFree(b);
     if (t->h_flags) cudaFreeHost(t->h_flags);
@@ -338,7 +344,7 @@ int gsb_tracker_run(gsb_tracker* t, int n_iters, int poll_every, int use_graph, 
     TCK(cudaMemcpyAsync(t->h_flags + t->C, t->n_isects, sizeof(int) * 2, cudaMemcpyDeviceToHost, t->stream), "flags");
     TCK(cudaStreamSynchronize(t->stream), "run sync");
     TCK(cudaGetLastError(), "run");
-    t->total_launches += (int64_t)done * kLaunchesPerIter;
+    t->total_launches += (int64_t)done * n_launches_per_iter(t);
     t->last_n_isects = t->h_flags[t->C];
     if (iters_done) *iters_done = done;
     if (elapsed_ms) TCK(cudaEventElapsedTime(elapsed_ms, t->ev0, t->ev1), "elapsed");
@@ -358,21 +364,21 @@ int gsb_tracker_profile(gsb_tracker* t, int n_iters, float* stage_ms_host) {
         int rc = ensure_capacity(t);
         if (rc) return rc;
     }
-    cudaEvent_t marks[kLaunchesPerIter + 1];
+    cudaEvent_t marks[kStages + 1];
     for (auto& m : marks) TCK(cudaEventCreate(&m), "event");
-    for (int k = 0; k < kLaunchesPerIter; ++k) stage_ms_host[k] = 0.f;
+    for (int k = 0; k < kStages; ++k) stage_ms_host[k] = 0.f;
     for (int it = 0; it < n_iters; ++it) {
         enqueue_iteration(t, false, marks);
         TCK(cudaStreamSynchronize(t->stream), "profile sync");
-        for (int k = 0; k < kLaunchesPerIter; ++k) {
+        for (int k = 0; k < kStages; ++k) {
             float ms = 0.f;
             TCK(cudaEventElapsedTime(&ms, marks[k], marks[k + 1]), "elapsed");
             stage_ms_host[k] += ms;
         }
     }
-    for (int k = 0; k < kLaunchesPerIter; ++k) stage_ms_host[k] /= (float)n_iters;
+    for (int k = 0; k < kStages; ++k) stage_ms_host[k] /= (float)n_iters;
     for (auto& m : marks) cudaEventDestroy(m);
-    t->total_launches += (int64_t)n_iters * kLaunchesPerIter;
+    t->total_launches += (int64_t)n_iters * n_launches_per_iter(t);
     TCK(cudaMemcpyAsync(t->h_flags + t->C, t->n_isects, sizeof(int) * 2, cudaMemcpyDeviceToHost, t->stream), "flags");
     TCK(cudaStreamSynchronize(t->stream), "profile sync");
     t->last_n_isects = t->h_flags[t->C];
@@ -429,7 +435,7 @@ int gsb_tracker_get_counters(gsb_tracker* t, int64_t* n_isects, int64_t* capacit
     if (!t) return fail(GSB_ERR_ARG, "gsb_tracker_get_counters: null", cudaSuccess);
     if (n_isects) *n_isects = t->last_n_isects;
     if (capacity) *capacity = t->cap;
-    if (launches_per_iter) *launches_per_iter = kLaunchesPerIter;
+    if (launches_per_iter) *launches_per_iter = n_launches_per_iter(t);
     if (total_launches) *total_launches = t->total_launches;
     return GSB_OK;
 }

@@ -33,6 +33,7 @@ class TrackerConfig:
     far_plane: float = 1e10
     eps2d: float = 0.3
     radius_clip: float = 0.0
+    normal_mode: str = "reference"     # "reference": cosine over dim=1 as loss.py:93 computes it; "pixel": per pixel
 
     def to_c(self) -> _lib.TrackerConfig:
         c = _lib.TrackerConfig()
@@ -42,6 +43,7 @@ class TrackerConfig:
         c.depth_lambda, c.normal_lambda = self.depth_lambda, self.normal_lambda
         c.early_stop, c.patience, c.warmup = int(self.early_stop), int(self.patience), int(self.warmup)
         c.near_plane, c.far_plane, c.eps2d, c.radius_clip = self.near_plane, self.far_plane, self.eps2d, self.radius_clip
+        c.normal_mode = {"off": 0, "pixel": 1, "reference": 2}[self.normal_mode]
         return c
 
 

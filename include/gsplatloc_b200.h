@@ -91,10 +91,27 @@ int gsb_sh_bwd(int n, int K, int degree, const float* dirs, const float* coeffs,
  * apply_mask: B = gt * (depth != 0) as the trainer does; 0: inputs are already masked.
  * -> sums_host-free: loss_sums[C,2] = {sum|A-B|, sum|E(A)-E(B)|} (divide by H*W for the means) and
  * v_depth[C,H,W] = w_d * dLd/ddepth + w_s * dLs/ddepth with w_* INCLUDING the 1/(H*W).
- * partial_ws: 2*C*ceil(W/32)*ceil(H/8) floats. */
+ * partial_ws: 3*C*ceil(W/32)*ceil(H/8) floats. */
 int gsb_depth_edge_loss(int C, int width, int height, const float* depth, const float* gt, int gt_per_camera,
                         int apply_mask, float w_d, float w_s, float* loss_sums, float* v_depth, float* partial_ws,
                         void* stream);
+
+/* ---- the same plus compute_normal_consistency_loss (loss.py:62-101; depth_to_normal geometry.py:164-197,
+ * depth_to_points :138-161 = kornia depth_to_3d_v2): normals n(D) = normalize(cross(dP/dx, dP/dy)) of the
+ * back-projected, replicate-padded depth images, L_n = 1 - mean(cos(n(B), n(A))).
+ *   GSB_NORMAL_PIXEL     : cosine over xyz per pixel, mean over H*W (what the paper describes)
+ *   GSB_NORMAL_REFERENCE : cosine_similarity(dim=1) on [H,W,3] tensors = over the image WIDTH per (row, channel),
+ *                          mean over H*3 (what loss.py:93 computes)
+ * Ks[C,3,3] device. loss_sums[C,3] = {sum|A-B|, sum|E(A)-E(B)|, sum cos} (L_n = 1 - sum_cos/(H*W) or /(3H)).
+ * v_depth = w_d dLd + w_s dLs (w_* include 1/(H*W)) + lambda_n dLn (plain weight).
+ * ws: gsb_loss_workspace_floats(C, width, height) floats. */
+#define GSB_NORMAL_OFF 0
+#define GSB_NORMAL_PIXEL 1
+#define GSB_NORMAL_REFERENCE 2
+size_t gsb_loss_workspace_floats(int C, int width, int height);
+int gsb_depth_edge_normal_loss(int C, int width, int height, const float* depth, const float* gt, int gt_per_camera,
+                               int apply_mask, const float* Ks, float w_d, float w_s, float lambda_n,
+                               int normal_mode, float* loss_sums, float* v_depth, float* ws, void* stream);
 
 /* ================= device-resident pose optimisation loop (Runner.train inner loop) ================= */
 
@@ -109,6 +126,8 @@ typedef struct gsb_tracker_config {
     int patience;                  /* 200, base.py:35 */
     int warmup;                    /* best-loss tracking starts when step > 100, gs_trainer_total.py:171 */
     float eps2d, near_plane, far_plane, radius_clip; /* 0.3, 1e-2, 1e10, 0 (model.py:119-133, A.1) */
+    int normal_mode;               /* GSB_NORMAL_*: how the cosine of the normal term is reduced (used when
+                                      normal_lambda != 0); default GSB_NORMAL_REFERENCE (loss.py:93) */
 } gsb_tracker_config;
 
 /* One per camera / pose hypothesis.  Mirrors CameraOptModule_quat_tans + its two Adam states + the early-stop

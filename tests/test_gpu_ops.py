@@ -317,3 +317,38 @@ def test_depth_edge_loss_kernel(ops, W, H):
     assert abs(float(Ld_c[0]) - float(Ld)) / float(Ld) < 1e-5
     assert abs(float(Ls_c[0]) - float(Ls)) / float(Ls) < 1e-5
     assert U.rel_err(v[0].cpu().numpy(), do.grad.numpy()) < 1e-4
+
+
+@pytest.mark.parametrize("mode,dim", [("pixel", -1), ("reference", 1)])
+@pytest.mark.parametrize("W,H", [(160, 96), (37, 21), (64, 8)])
+def test_normal_consistency_loss_kernel(ops, mode, dim, W, H):
+    """compute_normal_consistency_loss (loss.py:62-101) fused with the depth and edge terms: values and
+    d(total)/d(depth) against the oracle (fp64 autograd); tolerance 1e-4 relative on the loss, 1e-3 on the gradient."""
+    from gsplatloc_b200 import losses
+    g = torch.Generator().manual_seed(15)
+    yy, xx = torch.meshgrid(torch.arange(H, dtype=torch.float64), torch.arange(W, dtype=torch.float64), indexing="ij")
+    d = 2.0 + 0.01 * xx + 0.02 * yy + 0.2 * torch.sin(xx / 7.0) * torch.cos(yy / 5.0)     # smooth surface + holes
+    d[torch.rand(H, W, generator=g) < 0.05] = 0.0
+    gt = d + 0.05 * torch.sin(xx / 3.0 + yy / 4.0) + 0.01 * torch.randn(H, W, generator=g, dtype=torch.float64)
+    K = torch.tensor([[W * 0.5, 0, W / 2 - 0.5], [0, W * 0.5, H / 2 - 0.5], [0, 0, 1]], dtype=torch.float64)
+    do = d.clone().requires_grad_(True)
+    tot, Ld, Ls, Ln = orc.losses(do, gt, K, depth_lambda=0.7, normal_lambda=0.1, normal_dim=dim)
+    tot.backward()
+    Ld_c, Ls_c, Ln_c, v = losses.depth_edge_normal_loss(d.float().cuda()[None], gt.float().cuda(), K.float().cuda(),
+                                                        depth_lambda=0.7, normal_lambda=0.1, normal_mode=mode)
+    assert abs(float(Ld_c[0]) - float(Ld)) / float(Ld) < 1e-5
+    assert abs(float(Ls_c[0]) - float(Ls)) / float(Ls) < 1e-5
+    assert abs(float(Ln_c[0]) - float(Ln)) / abs(float(Ln)) < 1e-4, (float(Ln_c[0]), float(Ln))
+    assert U.rel_err(v[0].cpu().numpy(), do.grad.numpy()) < 1e-3
+    # the normal term alone, through the reference-named entry point (autograd in depth_rendered)
+    dr = d.float().cuda().requires_grad_(True)
+    mask = (d != 0).to(torch.float64)
+    loss = losses.compute_normal_consistency_loss((gt * mask).float().cuda(), dr, K=K.float().cuda(), reduce=mode)
+    loss.backward()
+    do2 = d.clone().requires_grad_(True)
+    ref = 1 - torch.nn.functional.cosine_similarity(orc.depth_to_normal(gt * mask, K), orc.depth_to_normal(do2, K),
+                                                    dim=dim).mean()
+    ref.backward()
+    assert abs(float(loss) - float(ref)) / abs(float(ref)) < 1e-4
+    gref = do2.grad.numpy() * (d.numpy() != 0)     # the kernel masks nothing here (apply_mask=False): compare on valid
+    assert U.rel_err(dr.grad.cpu().numpy() * (d.numpy() != 0), gref) < 1e-3

@@ -244,3 +244,26 @@ def test_full_size_properties_replica_200k(gsb):
             assert hist[-1, 0] < hist[0, 0] and hist[-1, 4] < hist[0, 4], "loss and eT go down"
         trk.close()
     assert np.float32(losses[0]).view(np.uint32) == np.float32(losses[1]).view(np.uint32)
+
+
+@pytest.mark.parametrize("mode,dim", [("pixel", -1), ("reference", 1)])
+def test_one_iteration_with_normal_term_matches_oracle(gsb, mode, dim):
+    """BASELINE.json configs[3]: depth + edge + normal loss (lambda = 0.7 / 0.2 / 0.1), pose gradient within 1e-3."""
+    fp = U.frame(U.SMALL_CAM, stride=2, seed=11)
+    c2w0 = _start_pose(fp)
+    trk = _tracker(gsb, fp, c2w0, fp.src_depth, early_stop=False, depth_lambda=0.7, normal_lambda=0.1, normal_mode=mode)
+    trk.run(1, poll_every=0, use_graph=False)
+    st = trk.states()[0]
+    dt = torch.float64
+    means, quats, scales, opac = U.map_tensors(fp, dt)
+    q = torch.tensor(orc.rotmat_to_quat(c2w0[:3, :3]), dtype=dt).requires_grad_(True)
+    t = torch.tensor(c2w0[:3, 3], dtype=dt).requires_grad_(True)
+    tot, Ld, Ls, Ln, d, a, meta = orc.pose_loss(q, t, means, quats, scales, opac, torch.as_tensor(fp.src_depth, dtype=dt),
+                                                 torch.tensor(fp.K, dtype=dt), fp.W, fp.H, 0.7, 0.1, dim)
+    tot.backward()
+    assert abs(st["normal_loss"] - float(Ln)) / abs(float(Ln)) < 1e-4, (st["normal_loss"], float(Ln))
+    assert abs(st["loss"] - float(tot)) / float(tot) < 1e-4
+    assert U.rel_err(st["g_q"], q.grad.numpy()) < 1e-3, (st["g_q"], q.grad)
+    assert U.rel_err(st["g_t"], t.grad.numpy()) < 1e-3, (st["g_t"], t.grad)
+    assert trk.counters()["launches_per_iter"] == (10 if mode == "reference" else 9)
+    trk.close()
