@@ -267,3 +267,44 @@ def test_one_iteration_with_normal_term_matches_oracle(gsb, mode, dim):
     assert U.rel_err(st["g_t"], t.grad.numpy()) < 1e-3, (st["g_t"], t.grad)
     assert trk.counters()["launches_per_iter"] == (10 if mode == "reference" else 9)
     trk.close()
+
+
+@pytest.mark.parametrize("tag,dl,nl", [("A", 0.8, 0.0), ("B", 0.7, 0.1)])
+def test_tracker_follows_the_reference_loop_fixture(gsb, tag, dl, nl):
+    """tests/golden/ref_loop_small.npz: GsplatLoc's own loop code (pose module, losses, Adam, schedulers, metrics)
+    run step by step on the CPU (make_golden.py).  The CUDA tracker must walk the same trajectory: loss within 1e-4
+    relative, pose gradients within 1e-3 relative, parameters within 5e-6 absolute after every Adam step."""
+    import os
+    gold = dict(np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_loop_small.npz")))
+    W, H = int(gold["cam"][0]), int(gold["cam"][1])
+    N = gold["means"].shape[0]
+    trk = gsb.PoseTracker(W, H, 1, gsb.TrackerConfig(max_steps=int(gold["max_steps"]), early_stop=False,
+                                                     depth_lambda=dl, normal_lambda=nl, normal_mode="reference"))
+    trk.set_map(torch.tensor(gold["means"]).cuda(), torch.tensor([[1.0, 0, 0, 0]]).repeat(N, 1).cuda(),
+                torch.tensor(gold["scales"]).cuda(), torch.ones(N).cuda())
+    trk.set_observation(torch.tensor(gold["gt_depth"]).cuda(), gold["K"])
+    trk.set_poses(gold["c2w_init"], gold["c2w_gt"])
+    n = gold[tag + "_quat"].shape[0]
+    for s in range(n):
+        st0 = trk.states()[0]
+        assert np.allclose(st0["q"], gold[tag + "_quat"][s], atol=5e-6), (s, st0["q"], gold[tag + "_quat"][s])
+        assert np.allclose(st0["t"], gold[tag + "_t"][s], atol=5e-6)
+        trk.run(1, poll_every=0, use_graph=(s % 2 == 1))
+        st = trk.states()[0]
+        assert abs(st["loss"] - gold[tag + "_total"][s]) / gold[tag + "_total"][s] < 1e-4
+        assert abs(st["depth_loss"] - gold[tag + "_Ld"][s]) / gold[tag + "_Ld"][s] < 1e-4
+        assert abs(st["edge_loss"] - gold[tag + "_Ls"][s]) / gold[tag + "_Ls"][s] < 1e-4
+        if nl:
+            assert abs(st["normal_loss"] - gold[tag + "_Ln"][s]) / gold[tag + "_Ln"][s] < 1e-4
+        assert U.rel_err(st["g_q"], gold[tag + "_g_quat"][s]) < 1e-3
+        assert U.rel_err(st["g_t"], gold[tag + "_g_t"][s]) < 1e-3
+        assert abs(st["eT"] - gold[tag + "_eT"][s]) < 1e-5 and abs(st["eR"] - gold[tag + "_eR"][s]) < 1e-2
+        assert abs(st["lr_q"] - gold[tag + "_lr_q"][min(s + 1, n - 1)]) < 1e-9 or s == n - 1
+        if s == 0:
+            d, a = trk.render()
+            assert U.rel_err(d[0].cpu().numpy(), gold[tag + "_first_depth"]) < 1e-4
+            assert U.rel_err(a[0].cpu().numpy(), gold[tag + "_first_alpha"]) < 1e-4
+    stf = trk.states()[0]
+    assert np.allclose(stf["q"], gold[tag + "_final_quat"], atol=5e-6)
+    assert np.allclose(stf["t"], gold[tag + "_final_t"], atol=5e-6)
+    trk.close()
