@@ -136,7 +136,7 @@ def rendered_observation(trk_cls, fp, device, stream=None):
 
 def run_native(args, rank, world, local_rank):
     import torch.distributed as dist
-    from gsplatloc_b200 import PoseTracker, TrackerConfig, _lib
+    from gsplatloc_b200 import PoseTracker, TrackerConfig, _lib, sharding
     if not torch.cuda.is_available():
         raise RuntimeError("bench.py needs a CUDA device: gsplatloc_b200 has no CPU path")
     _lib.lib()  # fail loudly if the extension is not built
@@ -202,10 +202,7 @@ def run_native(args, rank, world, local_rank):
     ms = e0.elapsed_time(e1)
     clocks = sampler.stop(wall0, wall1) if sampler else None
     launches = sum(t.counters()["total_launches"] for t in trackers) - launches0
-    records = []
-    for i, (t, fp) in enumerate(zip(trackers, frames)):
-        st = t.states()[0]
-        records.append([rank, i, st["eT"], st["eR"], st["loss"], *st["q"], *st["t"]])
+    records = [sharding.state_to_record(i * world + rank, rank, t.states()[0]) for i, t in enumerate(trackers)]
     M = int(np.mean([t.counters()["n_isects"] for t in trackers]))
 
     # ---------------------------------------------------------------- end-to-end leg (host buffers)
@@ -235,13 +232,10 @@ def run_native(args, rank, world, local_rank):
         tt = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         ms, ms_e2e = float(tt[0]), float(tt[1])
-        rec = torch.tensor(records, device=dev, dtype=torch.float32)
-        gathered = [torch.empty_like(rec) for _ in range(world)]
-        dist.all_gather(gathered, rec)                                           # final gather of pose errors (NCCL)
-        records = torch.cat(gathered).cpu().tolist()
         lt = torch.tensor([launches], device=dev, dtype=torch.float64)
         dist.all_reduce(lt)
         launches = int(lt[0])
+    records = sharding.gather_records(records, dev)        # the path's one collective: final gather of pose errors
     if rank != 0:
         return
     total_iters = K * iters * world
@@ -256,7 +250,6 @@ def run_native(args, rank, world, local_rank):
                   "alg_GBps": round(algorithmic_bytes(k, 1, N, M, P, T) / (v * 1e-3) / 1e9, 1) if v > 0 else None}
               for k, v in stage_ms.items()}
     iter_bytes = sum(algorithmic_bytes(k, 1, N, M, P, T) for k in stage_ms)
-    eT = np.array([r[2] for r in records]); eR = np.array([r[3] for r in records])
     out = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W_,
         "ms_per_step": round(ms / K, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -279,8 +272,7 @@ def run_native(args, rank, world, local_rank):
                                    "achieved_GBps": round(iter_bytes / (sum_ms * 1e-3) / 1e9, 1),
                                    "frac": round(iter_bytes / (sum_ms * 1e-3) / 1e9 / peak, 4)},
                      "stages": stages},
-        "pose_errors": {"frames": len(records), "ATE_rmse_m": float(np.sqrt((eT ** 2).mean())),
-                        "AAE_rmse_deg": float(np.sqrt((eR ** 2).mean()))},
+        "pose_errors": sharding.trajectory_errors(records),
     }
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(traffic_file):

@@ -92,7 +92,8 @@ struct LiftCtx {
 // accumulated into this thread's column of s_pose[12][BWD_BATCH].  Out of line on purpose: the camera, the
 // re-projection temporaries and the accumulators must not compete for registers with the replay loop.
 __device__ __noinline__ void lift_to_pose(const LiftCtx* __restrict__ ctx, int flat_id, float g0, float g1, float g2,
-                                          float g3, float g4, float g5, float* __restrict__ pose_col) {
+                                          float g3, float g4, float g5, float* __restrict__ pose_col,
+                                          int col_stride) {
     const Cam camera = ctx->cam;
     const int n = flat_id - ctx->cam_index * ctx->N;
     const float mean[3] = {__ldg(ctx->means + n * 3), __ldg(ctx->means + n * 3 + 1), __ldg(ctx->means + n * 3 + 2)};
@@ -107,7 +108,7 @@ __device__ __noinline__ void lift_to_pose(const LiftCtx* __restrict__ ctx, int f
     project_vjp(camera, p, Sc, g0, g1, g2, g3, g4, g5, v_pc, vS);
     pose_accumulate(camera, mean, S, v_pc, vS, acc, acc + 9);
 #pragma unroll
-    for (int k = 0; k < 12; ++k) pose_col[k * BWD_BATCH] += acc[k];
+    for (int k = 0; k < 12; ++k) pose_col[k * col_stride] += acc[k];
 }
 
 template <int CDIM, bool PACKED, bool LIFT>
@@ -304,7 +305,8 @@ __global__ void __launch_bounds__(256, LIFT ? 4 : 2) raster_bwd_kernel(
                 bool any = false;
 #pragma unroll
                 for (int k = 0; k < 6; ++k) any |= (gsum[k] != 0.f);
-                if (any) lift_to_pose(&s_ctx, s_id[tid], gsum[0], gsum[1], gsum[2], gsum[3], gsum[4], gsum[5], s_pose + tid);
+                if (any) lift_to_pose(&s_ctx, s_id[tid], gsum[0], gsum[1], gsum[2], gsum[3], gsum[4], gsum[5], s_pose + tid,
+                                      BWD_BATCH);
             }
         }
     }
@@ -322,6 +324,151 @@ __global__ void __launch_bounds__(256, LIFT ? 4 : 2) raster_bwd_kernel(
     }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Tracker path, second generation: every warp is an independent unit (no __syncthreads in the replay).
+//
+// The block-cooperative kernel above spends ~40 % of its stall samples at the barrier that closes each staged batch
+// (profiles/r1_c_iteration_full.md): the eight 8x4 patches of a tile finish their share of a batch at different times
+// and everybody waits for the slowest.  Here a warp walks the tile's sorted list on its own, back to front from ITS
+// last composited entry, 32 entries at a time: lane l gathers entry l, tests it against the warp's patch
+// (patch_mask), a ballot gives the entries to replay, each replayed entry is read back from a 1 KB per-warp staging
+// area.  The six per-Gaussian sums leave the butterfly reduction into a per-warp queue; when 32 are queued every lane
+// lifts one of them through the projection Jacobian (A.6) into its own 12 pose accumulators.  The lift is linear in
+// the six sums, so lifting per-warp partial sums is exact; it costs more lifts (one per (patch, Gaussian) instead of
+// one per (tile, Gaussian)) but no barrier, no zeroing of slot arrays and no cross-warp summation.  Order of every
+// floating-point sum is fixed -> deterministic, as before.  One partial (12 floats) per tile leaves the block.
+struct WarpScratch {
+    float4 rec[32][2];   // staged entries {x, y, a, b}, {c, opacity, depth, -}
+    int gid[32];         // their flat Gaussian ids
+    float qsum[64][6];   // lift queue (ring of 64): v_xy[2], v_conic[3], v_depth
+    int qid[64];
+};
+
+__global__ void __launch_bounds__(256, 4) raster_bwd_warp_kernel(
+    int C, int N, int W, int H, int tile_w, int tile_h, const float4* __restrict__ rec,
+    const int* __restrict__ tile_offsets, const int* __restrict__ n_isects_dev, const int* __restrict__ flatten_ids,
+    const float* __restrict__ render_alphas, const int* __restrict__ last_ids, const float* __restrict__ v_depth,
+    const float* __restrict__ v_alpha_img, const float* __restrict__ means, const float* __restrict__ quats,
+    const float* __restrict__ scales, const float* __restrict__ viewmats, const float* __restrict__ Ks, float eps2d,
+    float* __restrict__ partials, const int* __restrict__ stop) {
+    __shared__ WarpScratch s_w[8];
+    __shared__ float s_pose[12 * 256];
+    __shared__ LiftCtx s_ctx;
+
+    const int cam = blockIdx.z;
+    if (stop && stop[cam]) return;
+    const int tile_id = blockIdx.y * tile_w + blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int j = blockIdx.x * 16 + (wid & 1) * 8 + (lane & 7);
+    const int i = blockIdx.y * 16 + (wid >> 1) * 4 + (lane >> 3);
+    const float px = (float)j + 0.5f, py = (float)i + 0.5f;
+    const float tile_x0 = (float)(blockIdx.x * 16), tile_y0 = (float)(blockIdx.y * 16);
+    const bool inside = (i < H) && (j < W);
+    const size_t pix = ((size_t)cam * H + min(i, H - 1)) * W + min(j, W - 1);
+    const int bin = cam * tile_w * tile_h + tile_id;
+    const int range_start = tile_offsets[bin];
+    const int range_end = (bin == C * tile_w * tile_h - 1) ? *n_isects_dev : tile_offsets[bin + 1];
+
+    if (tid == 0) {
+        s_ctx.cam = load_cam(viewmats + cam * 16, Ks + cam * 9);
+        s_ctx.means = means; s_ctx.quats = quats; s_ctx.scales = scales;
+        s_ctx.W = W; s_ctx.H = H; s_ctx.N = N; s_ctx.cam_index = cam; s_ctx.eps2d = eps2d;
+    }
+#pragma unroll
+    for (int k = 0; k < 12; ++k) s_pose[k * 256 + tid] = 0.f;
+    __syncthreads();
+
+    const float T_final = inside ? 1.f - render_alphas[pix] : 1.f;
+    float T = T_final, buffer = 0.f;
+    const float v_rc = inside ? v_depth[pix] : 0.f;
+    const float v_ra_T = inside ? T_final * v_alpha_img[pix] : 0.f;
+    const int bin_final = inside ? last_ids[pix] : -1;
+    int warp_bin_final = bin_final;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) warp_bin_final = max(warp_bin_final, __shfl_xor_sync(0xffffffffu, warp_bin_final, o));
+
+    WarpScratch& ws = s_w[wid];
+    const int ridx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);   // see warp_reduce_multi<8>
+    const bool q_writer = ((lane & 3) == 0) && ridx < 6;
+    float* const pose_col = s_pose + tid;
+    int q_head = 0, q_tail = 0;   // ring indices (uniform across the warp)
+
+    // entries behind the warp's last composited one were composited by none of its pixels
+    const int first = min(range_end - 1, warp_bin_final);
+    for (int top = first; top >= range_start; top -= 32) {
+        const int pos = top - lane;
+        unsigned hit = 0u;
+        if (pos >= range_start) {
+            const int g = flatten_ids[pos];
+            const float4 r0 = __ldg(rec + 2 * (size_t)g), r1 = __ldg(rec + 2 * (size_t)g + 1);
+            ws.rec[lane][0] = make_float4(r0.x, r0.y, r1.x, r1.y);
+            ws.rec[lane][1] = make_float4(r1.z, r0.w, r0.z, 0.f);
+            ws.gid[lane] = g;
+            hit = (patch_mask(r0.x, r0.y, r1.x, r1.y, r1.z, r0.w, tile_x0, tile_y0) >> wid) & 1u;
+        }
+        unsigned bits = __ballot_sync(0xffffffffu, hit);
+        __syncwarp();
+        while (bits) {
+            const int t = __ffs(bits) - 1;
+            bits &= bits - 1;
+            const float4 p0 = ws.rec[t][0], p1 = ws.rec[t][1];
+            const float opac = p1.y;
+            const float dx = p0.x - px, dy = p0.y - py;
+            const float sigma = 0.5f * (p0.z * dx * dx + p1.x * dy * dy) + p0.w * dx * dy;
+            const float vis = exp_neg_fast(sigma);
+            const float alpha = fminf(GSB_ALPHA_MAX, opac * vis);
+            const bool valid = (top - t <= bin_final) && !(sigma < 0.f || alpha < GSB_ALPHA_MIN);
+            if (!__any_sync(0xffffffffu, valid)) continue;
+            float v[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] = 0.f;
+            if (valid) {
+                const float ra = rcp_fast(1.f - alpha);   // 1 - alpha >= 1e-3
+                T *= ra;
+                const float fac = alpha * T;
+                v[5] = fac * v_rc;
+                const float v_al = (p1.z * T - buffer * ra) * v_rc + v_ra_T * ra;
+                if (opac * vis <= GSB_ALPHA_MAX) {
+                    const float v_sigma = -opac * vis * v_al;
+                    v[2] = 0.5f * v_sigma * dx * dx;
+                    v[3] = v_sigma * dx * dy;
+                    v[4] = 0.5f * v_sigma * dy * dy;
+                    v[0] = v_sigma * (p0.z * dx + p0.w * dy);
+                    v[1] = v_sigma * (p0.w * dx + p1.x * dy);
+                }
+                buffer += p1.z * fac;
+            }
+            warp_reduce_multi<8>(v, lane);
+            const int slot = q_tail & 63;
+            if (q_writer) ws.qsum[slot][ridx] = v[0];
+            if (lane == 0) ws.qid[slot] = ws.gid[t];
+            ++q_tail;
+        }
+        __syncwarp();   // queue entries visible; staging area is rewritten by the next chunk
+        if (q_tail - q_head >= 32) {   // a chunk adds at most 32 entries: the ring of 64 never overflows
+            const int slot = (q_head + lane) & 63;
+            lift_to_pose(&s_ctx, ws.qid[slot], ws.qsum[slot][0], ws.qsum[slot][1], ws.qsum[slot][2], ws.qsum[slot][3],
+                         ws.qsum[slot][4], ws.qsum[slot][5], pose_col, 256);
+            q_head += 32;
+        }
+    }
+    __syncwarp();
+    if (lane < q_tail - q_head) {
+        const int slot = (q_head + lane) & 63;
+        lift_to_pose(&s_ctx, ws.qid[slot], ws.qsum[slot][0], ws.qsum[slot][1], ws.qsum[slot][2], ws.qsum[slot][3],
+                     ws.qsum[slot][4], ws.qsum[slot][5], pose_col, 256);
+    }
+    __syncthreads();
+    // 12 numbers x 256 thread columns -> one 12-float partial of this tile (fixed order: deterministic)
+    for (int k = wid; k < 12; k += 8) {
+        float s = 0.f;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) s += s_pose[k * 256 + q * 32 + lane];
+        s = warp_sum(s);
+        if (lane == 0) partials[(size_t)bin * 12 + k] = s;
+    }
+}
+
 void launch_raster_bwd_lift(int C, int N, int W, int H, int tile_w, int tile_h, const float4* rec,
                             const int* tile_offsets, const int* n_isects_dev, const int* flatten_ids,
                             const float* render_alphas, const int* last_ids, const float* v_depth,
@@ -330,10 +477,9 @@ void launch_raster_bwd_lift(int C, int N, int W, int H, int tile_w, int tile_h, 
                             cudaStream_t st) {
     if (C * tile_w * tile_h == 0) return;
     dim3 grid(tile_w, tile_h, C);
-    raster_bwd_kernel<1, true, true><<<grid, 256, 0, st>>>(
-        C, N, W, H, tile_w, tile_h, rec, nullptr, nullptr, nullptr, nullptr, nullptr, tile_offsets, n_isects_dev, 0,
-        flatten_ids, render_alphas, last_ids, v_depth, v_alpha, nullptr, nullptr, nullptr, nullptr, means, quats,
-        scales, viewmats, Ks, eps2d, partials, stop);
+    raster_bwd_warp_kernel<<<grid, 256, 0, st>>>(C, N, W, H, tile_w, tile_h, rec, tile_offsets, n_isects_dev,
+                                                 flatten_ids, render_alphas, last_ids, v_depth, v_alpha, means, quats,
+                                                 scales, viewmats, Ks, eps2d, partials, stop);
 }
 
 int launch_raster_bwd_soa(int cdim, int C, int N, int W, int H, int tile_w, int tile_h, const float* means2d,
