@@ -469,6 +469,233 @@ __global__ void __launch_bounds__(256, 4) raster_bwd_warp_kernel(
     }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Tracker path, third generation: "quad-scan" replay.
+//
+// The pixel-per-lane replay above spends a third of its instructions on the 32-lane butterfly that sums six numbers
+// per Gaussian, and evaluates one (pixel, Gaussian) pair per lane per ~120 warp instructions.  Here the warp's 8x4
+// patch is re-mapped: lane L = (column pr = L >> 2, Gaussian pair gq = L & 3) owns the FOUR pixels of column pr and
+// TWO of the eight Gaussians of a step, i.e. 8 pairs per lane per step with all Gaussian data in registers.
+//   * The sequential recurrences of A.5 along the Gaussian axis (T <- T / (1 - alpha), buffer <- buffer + d alpha T)
+//     become a two-element local combine plus a 4-lane scan (2 shuffles) and a 4-lane broadcast per pixel.
+//   * dx is shared by a lane's four pixels, so the five geometric gradients reduce to three moments of v_sigma
+//     (sum v, sum v dy, sum v dy^2) accumulated in registers; only once per step are 12 numbers (2 Gaussians x 6) summed
+//     over the eight columns (12 shuffles for 256 pairs instead of 9 per 32 pairs).
+// The set of (pixel, Gaussian) pairs evaluated, the validity rules and every formula are those of the replay above;
+// only the association order of the per-pixel products / sums differs (1e-7 relative).  Entries are first compacted
+// (patch_mask) into a per-warp ring; a step consumes eight; the summed gradients go to the lift ring as before.
+struct QuadScratch {
+    float4 rec[64][2];   // compacted entries {x, y, a', b'}, {c', opacity, depth, position bits}; a' = -log2(e)/2 * a ...
+    int gid[64];
+    float qsum[64][6];   // lift ring: v_xy[2], v_conic[3], v_depth
+    int qid[64];
+};
+
+#define GSB_NEG_LOG2E -1.4426950408889634f
+
+__global__ void __launch_bounds__(256, 2) raster_bwd_quad_kernel(
+    int C, int N, int W, int H, int tile_w, int tile_h, const float4* __restrict__ rec,
+    const int* __restrict__ tile_offsets, const int* __restrict__ n_isects_dev, const int* __restrict__ flatten_ids,
+    const float* __restrict__ render_alphas, const int* __restrict__ last_ids, const float* __restrict__ v_depth,
+    const float* __restrict__ v_alpha_img, const float* __restrict__ means, const float* __restrict__ quats,
+    const float* __restrict__ scales, const float* __restrict__ viewmats, const float* __restrict__ Ks, float eps2d,
+    float* __restrict__ partials, const int* __restrict__ stop) {
+    __shared__ QuadScratch s_w[8];
+    __shared__ float s_pose[12 * 256];
+    __shared__ LiftCtx s_ctx;
+
+    const int cam = blockIdx.z;
+    if (stop && stop[cam]) return;
+    const int tile_id = blockIdx.y * tile_w + blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int gq = lane & 3, pr = lane >> 2;
+    const int j = blockIdx.x * 16 + (wid & 1) * 8 + pr;          // this lane's pixel column
+    const int i0 = blockIdx.y * 16 + (wid >> 1) * 4;              // first row of the patch
+    const float px = (float)j + 0.5f, py0 = (float)i0 + 0.5f;
+    const float tile_x0 = (float)(blockIdx.x * 16), tile_y0 = (float)(blockIdx.y * 16);
+    const int bin = cam * tile_w * tile_h + tile_id;
+    const int range_start = tile_offsets[bin];
+    const int range_end = (bin == C * tile_w * tile_h - 1) ? *n_isects_dev : tile_offsets[bin + 1];
+
+    if (tid == 0) {
+        s_ctx.cam = load_cam(viewmats + cam * 16, Ks + cam * 9);
+        s_ctx.means = means; s_ctx.quats = quats; s_ctx.scales = scales;
+        s_ctx.W = W; s_ctx.H = H; s_ctx.N = N; s_ctx.cam_index = cam; s_ctx.eps2d = eps2d;
+    }
+#pragma unroll
+    for (int k = 0; k < 12; ++k) s_pose[k * 256 + tid] = 0.f;
+    __syncthreads();
+
+    // state of the lane's four pixels (replicated in the four lanes of a column)
+    float T[4], buf[4], v_rc[4], v_raT[4];
+    int bin_final[4];
+    int warp_bin_final = -1;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const int i = i0 + r;
+        const bool inside = (i < H) && (j < W);
+        const size_t pix = ((size_t)cam * H + min(i, H - 1)) * W + min(j, W - 1);
+        const float Tf = inside ? 1.f - render_alphas[pix] : 1.f;
+        T[r] = Tf; buf[r] = 0.f;
+        v_rc[r] = inside ? v_depth[pix] : 0.f;
+        v_raT[r] = inside ? Tf * v_alpha_img[pix] : 0.f;
+        bin_final[r] = inside ? last_ids[pix] : -1;
+        warp_bin_final = max(warp_bin_final, bin_final[r]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) warp_bin_final = max(warp_bin_final, __shfl_xor_sync(0xffffffffu, warp_bin_final, o));
+
+    QuadScratch& ws = s_w[wid];
+    float* const pose_col = s_pose + tid;
+    int r_head = 0, r_tail = 0;   // compaction ring (uniform)
+    int q_head = 0, q_tail = 0;   // lift ring (uniform)
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const bool up16 = lane & 16, up8 = lane & 8;
+
+    const int first = min(range_end - 1, warp_bin_final);
+    int top = first;
+    bool more = top >= range_start;
+    while (more || r_tail - r_head > 0) {
+        if (more) {
+            // ---- gather 32 entries of the tile list (back to front), keep those that can reach this patch
+            const int pos = top - lane;
+            unsigned hit = 0u;
+            float4 e0, e1;
+            int g = 0;
+            if (pos >= range_start) {
+                g = flatten_ids[pos];
+                const float4 r0 = __ldg(rec + 2 * (size_t)g), r1 = __ldg(rec + 2 * (size_t)g + 1);
+                hit = (patch_mask(r0.x, r0.y, r1.x, r1.y, r1.z, r0.w, tile_x0, tile_y0) >> wid) & 1u;
+                e0 = make_float4(r0.x, r0.y, 0.5f * GSB_NEG_LOG2E * r1.x, GSB_NEG_LOG2E * r1.y);
+                e1 = make_float4(0.5f * GSB_NEG_LOG2E * r1.z, r0.w, r0.z, __int_as_float(pos));
+            }
+            const unsigned bits = __ballot_sync(0xffffffffu, hit);
+            if (hit) {
+                const int slot = (r_tail + __popc(bits & lt_mask)) & 63;
+                ws.rec[slot][0] = e0; ws.rec[slot][1] = e1; ws.gid[slot] = g;
+            }
+            r_tail += __popc(bits);
+            top -= 32;
+            more = top >= range_start;
+            __syncwarp();
+        }
+        // ---- consume steps of eight compacted entries (a partial last step is padded with dead entries)
+        while (r_tail - r_head >= 8 || (!more && r_tail - r_head > 0)) {
+            const int avail = r_tail - r_head;
+            const int sA = (r_head + 2 * gq) & 63, sB = (r_head + 2 * gq + 1) & 63;
+            float4 a0 = ws.rec[sA][0], a1 = ws.rec[sA][1], b0 = ws.rec[sB][0], b1 = ws.rec[sB][1];
+            if (2 * gq >= avail) { a0 = make_float4(0.f, 0.f, 0.f, 0.f); a1 = make_float4(0.f, 0.f, 0.f, __int_as_float(0x7fffffff)); }
+            if (2 * gq + 1 >= avail) { b0 = make_float4(0.f, 0.f, 0.f, 0.f); b1 = make_float4(0.f, 0.f, 0.f, __int_as_float(0x7fffffff)); }
+            const int posA = __float_as_int(a1.w), posB = __float_as_int(b1.w);
+            // per-Gaussian terms shared by the four pixels of the column: sigma' = qa + dy * (qb + qc * dy)
+            const float dxA = a0.x - px, dxB = b0.x - px;
+            const float qaA = a0.z * dxA * dxA, qbA = a0.w * dxA, qaB = b0.z * dxB * dxB, qbB = b0.w * dxB;
+            const float dyA0 = a0.y - py0, dyB0 = b0.y - py0;
+            float mA0 = 0.f, mA1 = 0.f, mA2 = 0.f, mAd = 0.f, mB0 = 0.f, mB1 = 0.f, mB2 = 0.f, mBd = 0.f;
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const float dyA = dyA0 - (float)r, dyB = dyB0 - (float)r;
+                const float sgA = fmaf(dyA, fmaf(a1.x, dyA, qbA), qaA), sgB = fmaf(dyB, fmaf(b1.x, dyB, qbB), qaB);
+                float visA, visB;
+                asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(visA) : "f"(sgA));
+                asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(visB) : "f"(sgB));
+                const float ovA = a1.y * visA, ovB = b1.y * visB;
+                const float alA = fminf(GSB_ALPHA_MAX, ovA), alB = fminf(GSB_ALPHA_MAX, ovB);
+                const bool okA = (posA <= bin_final[r]) && !(sgA > 0.f) && !(alA < GSB_ALPHA_MIN);
+                const bool okB = (posB <= bin_final[r]) && !(sgB > 0.f) && !(alB < GSB_ALPHA_MIN);
+                const float wA = okA ? 1.f - alA : 1.f, wB = okB ? 1.f - alB : 1.f;   // 1/ra
+                const float raA = okA ? rcp_fast(wA) : 1.f, raB = okB ? rcp_fast(wB) : 1.f;
+                // inclusive scan of ra over the 8 Gaussians of the step: local pair, then the four lanes of the column
+                float inc = raA * raB;
+                float tsh = __shfl_up_sync(0xffffffffu, inc, 1, 4);
+                if (gq >= 1) inc *= tsh;
+                tsh = __shfl_up_sync(0xffffffffu, inc, 2, 4);
+                if (gq >= 2) inc *= tsh;
+                const float tot = __shfl_sync(0xffffffffu, inc, 3, 4);
+                const float TB = T[r] * inc;          // transmittance in front of B (after dividing B out)
+                const float TA = TB * wB;             // ... in front of A
+                T[r] *= tot;
+                const float facA = okA ? alA * TA : 0.f, facB = okB ? alB * TB : 0.f;
+                const float cA = a1.z * facA, cB = b1.z * facB;
+                float sinc = cA + cB;
+                float ssh = __shfl_up_sync(0xffffffffu, sinc, 1, 4);
+                if (gq >= 1) sinc += ssh;
+                ssh = __shfl_up_sync(0xffffffffu, sinc, 2, 4);
+                if (gq >= 2) sinc += ssh;
+                const float stot = __shfl_sync(0xffffffffu, sinc, 3, 4);
+                const float bufA = buf[r] + (sinc - (cA + cB));   // sum of everything replayed before A
+                const float bufB = bufA + cA;
+                buf[r] += stot;
+                const float valA = (a1.z * TA - bufA * raA) * v_rc[r] + v_raT[r] * raA;
+                const float valB = (b1.z * TB - bufB * raB) * v_rc[r] + v_raT[r] * raB;
+                const float vsA = (okA && ovA <= GSB_ALPHA_MAX) ? -ovA * valA : 0.f;   // v_sigma
+                const float vsB = (okB && ovB <= GSB_ALPHA_MAX) ? -ovB * valB : 0.f;
+                mAd = fmaf(facA, v_rc[r], mAd); mBd = fmaf(facB, v_rc[r], mBd);
+                mA0 += vsA; mB0 += vsB;
+                const float vdA = vsA * dyA, vdB = vsB * dyB;
+                mA1 += vdA; mB1 += vdB;
+                mA2 = fmaf(vdA, dyA, mA2); mB2 = fmaf(vdB, dyB, mB2);
+            }
+            // moments -> the six sums of this lane's column (conic back in its own units: a = a' / (-log2e/2) ...)
+            const float caA = a0.z * (2.f / GSB_NEG_LOG2E), cbA = a0.w * (1.f / GSB_NEG_LOG2E), ccA = a1.x * (2.f / GSB_NEG_LOG2E);
+            const float caB = b0.z * (2.f / GSB_NEG_LOG2E), cbB = b0.w * (1.f / GSB_NEG_LOG2E), ccB = b1.x * (2.f / GSB_NEG_LOG2E);
+            float v[12];
+            v[0] = caA * dxA * mA0 + cbA * mA1;  v[1] = cbA * dxA * mA0 + ccA * mA1;
+            v[2] = 0.5f * dxA * dxA * mA0;       v[3] = dxA * mA1;  v[4] = 0.5f * mA2;  v[5] = mAd;
+            v[6] = caB * dxB * mB0 + cbB * mB1;  v[7] = cbB * dxB * mB0 + ccB * mB1;
+            v[8] = 0.5f * dxB * dxB * mB0;       v[9] = dxB * mB1;  v[10] = 0.5f * mB2; v[11] = mBd;
+            // sum over the eight columns (lane bits 2..4): halve 12 -> 6 (A | B) -> 3, then a plain butterfly
+#pragma unroll
+            for (int k = 0; k < 6; ++k) {
+                const float keep = up16 ? v[k + 6] : v[k], send = up16 ? v[k] : v[k + 6];
+                v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+            }
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const float keep = up8 ? v[k + 3] : v[k], send = up8 ? v[k] : v[k + 3];
+                v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+            }
+#pragma unroll
+            for (int k = 0; k < 3; ++k) v[k] += __shfl_xor_sync(0xffffffffu, v[k], 4);
+            if (!(lane & 4)) {   // lane (gq, bit16 -> A|B, bit8 -> components 0..2 | 3..5) writes three numbers
+                const int e = 2 * gq + (up16 ? 1 : 0);
+                const int slot = (q_tail + e) & 63;
+                float* dst = &ws.qsum[slot][up8 ? 3 : 0];
+                dst[0] = v[0]; dst[1] = v[1]; dst[2] = v[2];
+                if (!up8) ws.qid[slot] = (e < avail) ? ws.gid[(r_head + e) & 63] : -1;
+            }
+            r_head += min(avail, 8);
+            q_tail += 8;
+            __syncwarp();
+            if (q_tail - q_head >= 32) {
+                const int slot = (q_head + lane) & 63;
+                const int gid = ws.qid[slot];
+                if (gid >= 0)
+                    lift_to_pose(&s_ctx, gid, ws.qsum[slot][0], ws.qsum[slot][1], ws.qsum[slot][2], ws.qsum[slot][3],
+                                 ws.qsum[slot][4], ws.qsum[slot][5], pose_col, 256);
+                q_head += 32;
+                __syncwarp();
+            }
+        }
+    }
+    __syncwarp();
+    if (lane < q_tail - q_head) {
+        const int slot = (q_head + lane) & 63;
+        const int gid = ws.qid[slot];
+        if (gid >= 0)
+            lift_to_pose(&s_ctx, gid, ws.qsum[slot][0], ws.qsum[slot][1], ws.qsum[slot][2], ws.qsum[slot][3],
+                         ws.qsum[slot][4], ws.qsum[slot][5], pose_col, 256);
+    }
+    __syncthreads();
+    for (int k = wid; k < 12; k += 8) {
+        float s = 0.f;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) s += s_pose[k * 256 + q * 32 + lane];
+        s = warp_sum(s);
+        if (lane == 0) partials[(size_t)bin * 12 + k] = s;
+    }
+}
+
 void launch_raster_bwd_lift(int C, int N, int W, int H, int tile_w, int tile_h, const float4* rec,
                             const int* tile_offsets, const int* n_isects_dev, const int* flatten_ids,
                             const float* render_alphas, const int* last_ids, const float* v_depth,
@@ -477,7 +704,7 @@ void launch_raster_bwd_lift(int C, int N, int W, int H, int tile_w, int tile_h, 
                             cudaStream_t st) {
     if (C * tile_w * tile_h == 0) return;
     dim3 grid(tile_w, tile_h, C);
-    raster_bwd_warp_kernel<<<grid, 256, 0, st>>>(C, N, W, H, tile_w, tile_h, rec, tile_offsets, n_isects_dev,
+    raster_bwd_quad_kernel<<<grid, 256, 0, st>>>(C, N, W, H, tile_w, tile_h, rec, tile_offsets, n_isects_dev,
                                                  flatten_ids, render_alphas, last_ids, v_depth, v_alpha, means, quats,
                                                  scales, viewmats, Ks, eps2d, partials, stop);
 }
