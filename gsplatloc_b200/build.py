@@ -34,7 +34,8 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
 
     def compile_one(name: str) -> str:
         obj = os.path.join(objdir, name + ".o")
-        cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, name + ".cu"), "-o", obj]
+        cmd = [nvcc, *NVCC_FLAGS, *os.environ.get("GSB_NVCC_EXTRA", "").split(), "-c",
+               os.path.join(CSRC, name + ".cu"), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         r = subprocess.run(cmd, capture_output=True, text=True)

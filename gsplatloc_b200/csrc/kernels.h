@@ -50,7 +50,8 @@ void launch_tile_sort(int C, int n_tiles, int tile_bits, const int* offsets, uin
 // ---- raster_fwd.cu / raster_bwd.cu
 void launch_raster_fwd_packed(int C, int W, int H, int tile_w, int tile_h, const float4* rec, const int* tile_offsets,
                               const int* n_isects_dev, const int* flatten_ids, float* render_depth,
-                              float* render_alphas, int* last_ids, int normalize, const int* stop, cudaStream_t st);
+                              float* render_alphas, int* last_ids, int normalize, const int* stop,
+                              unsigned char* masks_out, cudaStream_t st);
 int launch_raster_fwd_soa(int cdim, int C, int W, int H, int tile_w, int tile_h, const float* means2d,
                           const float* conics, const float* colors, const float* opacities, const float* backgrounds,
                           const int* tile_offsets, int n_isects, const int* flatten_ids, float* render_colors,
@@ -60,7 +61,7 @@ void launch_raster_bwd_lift(int C, int N, int W, int H, int tile_w, int tile_h, 
                             const float* render_alphas, const int* last_ids, const float* v_depth,
                             const float* v_alpha, const float* means, const float* quats, const float* scales,
                             const float* viewmats, const float* Ks, float eps2d, float* partials, const int* stop,
-                            cudaStream_t st);
+                            const unsigned char* masks, cudaStream_t st);
 int launch_raster_bwd_soa(int cdim, int C, int N, int W, int H, int tile_w, int tile_h, const float* means2d,
                           const float* conics, const float* colors, const float* opacities, const float* backgrounds,
                           const int* tile_offsets, int n_isects, const int* flatten_ids, const float* render_alphas,

@@ -492,14 +492,17 @@ struct QuadScratch {
 };
 
 #define GSB_NEG_LOG2E -1.4426950408889634f
+#ifndef GSB_BWD_OCC
+#define GSB_BWD_OCC 2   // resident blocks per SM the quad kernel is compiled for (128 registers)
+#endif
 
-__global__ void __launch_bounds__(256, 2) raster_bwd_quad_kernel(
+__global__ void __launch_bounds__(256, GSB_BWD_OCC) raster_bwd_quad_kernel(
     int C, int N, int W, int H, int tile_w, int tile_h, const float4* __restrict__ rec,
     const int* __restrict__ tile_offsets, const int* __restrict__ n_isects_dev, const int* __restrict__ flatten_ids,
     const float* __restrict__ render_alphas, const int* __restrict__ last_ids, const float* __restrict__ v_depth,
     const float* __restrict__ v_alpha_img, const float* __restrict__ means, const float* __restrict__ quats,
     const float* __restrict__ scales, const float* __restrict__ viewmats, const float* __restrict__ Ks, float eps2d,
-    float* __restrict__ partials, const int* __restrict__ stop) {
+    float* __restrict__ partials, const int* __restrict__ stop, const unsigned char* __restrict__ masks) {
     __shared__ QuadScratch s_w[8];
     __shared__ float s_pose[12 * 256];
     __shared__ LiftCtx s_ctx;
@@ -562,10 +565,11 @@ __global__ void __launch_bounds__(256, 2) raster_bwd_quad_kernel(
             unsigned hit = 0u;
             float4 e0, e1;
             int g = 0;
-            if (pos >= range_start) {
+            // the forward stored every staged entry's patch mask: non-reaching entries cost one byte load here
+            if (pos >= range_start) hit = ((unsigned)masks[pos] >> wid) & 1u;
+            if (hit) {
                 g = flatten_ids[pos];
                 const float4 r0 = __ldg(rec + 2 * (size_t)g), r1 = __ldg(rec + 2 * (size_t)g + 1);
-                hit = (patch_mask(r0.x, r0.y, r1.x, r1.y, r1.z, r0.w, tile_x0, tile_y0) >> wid) & 1u;
                 e0 = make_float4(r0.x, r0.y, 0.5f * GSB_NEG_LOG2E * r1.x, GSB_NEG_LOG2E * r1.y);
                 e1 = make_float4(0.5f * GSB_NEG_LOG2E * r1.z, r0.w, r0.z, __int_as_float(pos));
             }
@@ -600,11 +604,13 @@ __global__ void __launch_bounds__(256, 2) raster_bwd_quad_kernel(
                 asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(visA) : "f"(sgA));
                 asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(visB) : "f"(sgB));
                 const float ovA = a1.y * visA, ovB = b1.y * visB;
-                const float alA = fminf(GSB_ALPHA_MAX, ovA), alB = fminf(GSB_ALPHA_MAX, ovB);
-                const bool okA = (posA <= bin_final[r]) && !(sgA > 0.f) && !(alA < GSB_ALPHA_MIN);
-                const bool okB = (posB <= bin_final[r]) && !(sgB > 0.f) && !(alB < GSB_ALPHA_MIN);
-                const float wA = okA ? 1.f - alA : 1.f, wB = okB ? 1.f - alB : 1.f;   // 1/ra
-                const float raA = okA ? rcp_fast(wA) : 1.f, raB = okB ? rcp_fast(wB) : 1.f;
+                const float alA0 = fminf(GSB_ALPHA_MAX, ovA), alB0 = fminf(GSB_ALPHA_MAX, ovB);
+                const bool okA = (posA <= bin_final[r]) && !(sgA > 0.f) && !(alA0 < GSB_ALPHA_MIN);
+                const bool okB = (posB <= bin_final[r]) && !(sgB > 0.f) && !(alB0 < GSB_ALPHA_MIN);
+                // dead pairs get alpha = 0: every formula below then yields its neutral element without a branch
+                const float alA = okA ? alA0 : 0.f, alB = okB ? alB0 : 0.f;
+                const float wA = 1.f - alA, wB = 1.f - alB;             // 1 / ra  (>= 1e-3)
+                const float raA = rcp_fast(wA), raB = rcp_fast(wB);     // rcp(1) == 1
                 // inclusive scan of ra over the 8 Gaussians of the step: local pair, then the four lanes of the column
                 float inc = raA * raB;
                 float tsh = __shfl_up_sync(0xffffffffu, inc, 1, 4);
@@ -615,21 +621,23 @@ __global__ void __launch_bounds__(256, 2) raster_bwd_quad_kernel(
                 const float TB = T[r] * inc;          // transmittance in front of B (after dividing B out)
                 const float TA = TB * wB;             // ... in front of A
                 T[r] *= tot;
-                const float facA = okA ? alA * TA : 0.f, facB = okB ? alB * TB : 0.f;
+                const float facA = alA * TA, facB = alB * TB;
                 const float cA = a1.z * facA, cB = b1.z * facB;
-                float sinc = cA + cB;
+                const float loc = cA + cB;
+                float sinc = loc;
                 float ssh = __shfl_up_sync(0xffffffffu, sinc, 1, 4);
                 if (gq >= 1) sinc += ssh;
                 ssh = __shfl_up_sync(0xffffffffu, sinc, 2, 4);
                 if (gq >= 2) sinc += ssh;
                 const float stot = __shfl_sync(0xffffffffu, sinc, 3, 4);
-                const float bufA = buf[r] + (sinc - (cA + cB));   // sum of everything replayed before A
+                const float bufA = buf[r] + (sinc - loc);   // sum of everything replayed before A
                 const float bufB = bufA + cA;
                 buf[r] += stot;
                 const float valA = (a1.z * TA - bufA * raA) * v_rc[r] + v_raT[r] * raA;
                 const float valB = (b1.z * TB - bufB * raB) * v_rc[r] + v_raT[r] * raB;
-                const float vsA = (okA && ovA <= GSB_ALPHA_MAX) ? -ovA * valA : 0.f;   // v_sigma
-                const float vsB = (okB && ovB <= GSB_ALPHA_MAX) ? -ovB * valB : 0.f;
+                // v_sigma = -opac * vis * v_alpha, only where alpha is not clamped (A.5) and the pair is live
+                const float gA = (okA && ovA <= GSB_ALPHA_MAX) ? -ovA : 0.f, gB = (okB && ovB <= GSB_ALPHA_MAX) ? -ovB : 0.f;
+                const float vsA = gA * valA, vsB = gB * valB;
                 mAd = fmaf(facA, v_rc[r], mAd); mBd = fmaf(facB, v_rc[r], mBd);
                 mA0 += vsA; mB0 += vsB;
                 const float vdA = vsA * dyA, vdB = vsB * dyB;
@@ -701,12 +709,12 @@ void launch_raster_bwd_lift(int C, int N, int W, int H, int tile_w, int tile_h, 
                             const float* render_alphas, const int* last_ids, const float* v_depth,
                             const float* v_alpha, const float* means, const float* quats, const float* scales,
                             const float* viewmats, const float* Ks, float eps2d, float* partials, const int* stop,
-                            cudaStream_t st) {
+                            const unsigned char* masks, cudaStream_t st) {
     if (C * tile_w * tile_h == 0) return;
     dim3 grid(tile_w, tile_h, C);
     raster_bwd_quad_kernel<<<grid, 256, 0, st>>>(C, N, W, H, tile_w, tile_h, rec, tile_offsets, n_isects_dev,
                                                  flatten_ids, render_alphas, last_ids, v_depth, v_alpha, means, quats,
-                                                 scales, viewmats, Ks, eps2d, partials, stop);
+                                                 scales, viewmats, Ks, eps2d, partials, stop, masks);
 }
 
 int launch_raster_bwd_soa(int cdim, int C, int N, int W, int H, int tile_w, int tile_h, const float* means2d,

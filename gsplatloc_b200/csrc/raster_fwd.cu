@@ -49,7 +49,8 @@ __global__ void __launch_bounds__(256) raster_fwd_kernel(
     const float* __restrict__ conics, const float* __restrict__ colors, const float* __restrict__ opacities,
     const float* __restrict__ backgrounds, const int* __restrict__ tile_offsets, const int* __restrict__ n_isects_dev,
     int n_isects_host, const int* __restrict__ flatten_ids, float* __restrict__ render_colors,
-    float* __restrict__ render_alphas, int* __restrict__ last_ids, int normalize_last, const int* __restrict__ stop) {
+    float* __restrict__ render_alphas, int* __restrict__ last_ids, int normalize_last, const int* __restrict__ stop,
+    unsigned char* __restrict__ masks_out) {
     constexpr int RS = RecStride<CDIM>::value;
     __shared__ __align__(16) float sm[256 * RS];
     __shared__ unsigned char s_mask[256];
@@ -85,6 +86,7 @@ __global__ void __launch_bounds__(256) raster_fwd_kernel(
             m = stage_gaussian<CDIM, PACKED>(sm + tid * RS, flatten_ids[idx], rec, means2d, conics, colors, opacities,
                                              tile_x0, tile_y0);
         s_mask[tid] = (unsigned char)m;
+        if (masks_out && idx < range_end) masks_out[idx] = (unsigned char)m;   // reused by the backward's gather
         __syncthreads();
         if (warp_done) continue;
         const int batch_size = min(256, range_end - batch_start);
@@ -137,20 +139,22 @@ static void launch_t(int C, int W, int H, int tile_w, int tile_h, const float4* 
                      const float* conics, const float* colors, const float* opacities, const float* backgrounds,
                      const int* tile_offsets, const int* n_isects_dev, int n_isects_host, const int* flatten_ids,
                      float* render_colors, float* render_alphas, int* last_ids, int normalize_last, const int* stop,
-                     cudaStream_t st) {
+                     unsigned char* masks_out, cudaStream_t st) {
     dim3 grid(tile_w, tile_h, C);
     raster_fwd_kernel<CDIM, PACKED><<<grid, 256, 0, st>>>(C, W, H, tile_w, tile_h, rec, means2d, conics, colors,
                                                             opacities, backgrounds, tile_offsets, n_isects_dev,
                                                             n_isects_host, flatten_ids, render_colors, render_alphas,
-                                                            last_ids, normalize_last, stop);
+                                                            last_ids, normalize_last, stop, masks_out);
 }
 
 void launch_raster_fwd_packed(int C, int W, int H, int tile_w, int tile_h, const float4* rec, const int* tile_offsets,
                               const int* n_isects_dev, const int* flatten_ids, float* render_depth,
-                              float* render_alphas, int* last_ids, int normalize, const int* stop, cudaStream_t st) {
+                              float* render_alphas, int* last_ids, int normalize, const int* stop,
+                              unsigned char* masks_out, cudaStream_t st) {
     if (C * tile_w * tile_h == 0) return;
     launch_t<1, true>(C, W, H, tile_w, tile_h, rec, nullptr, nullptr, nullptr, nullptr, nullptr, tile_offsets,
-                      n_isects_dev, 0, flatten_ids, render_depth, render_alphas, last_ids, normalize, stop, st);
+                      n_isects_dev, 0, flatten_ids, render_depth, render_alphas, last_ids, normalize, stop, masks_out,
+                      st);
 }
 
 int launch_raster_fwd_soa(int cdim, int C, int W, int H, int tile_w, int tile_h, const float* means2d,
@@ -162,7 +166,7 @@ int launch_raster_fwd_soa(int cdim, int C, int W, int H, int tile_w, int tile_h,
     case D:                                                                                                     \
         launch_t<D, false>(C, W, H, tile_w, tile_h, nullptr, means2d, conics, colors, opacities, backgrounds,   \
                            tile_offsets, nullptr, n_isects, flatten_ids, render_colors, render_alphas, last_ids, \
-                           0, nullptr, st);                                                                     \
+                           0, nullptr, nullptr, st);                                                            \
         return 0;
     switch (cdim) {
         GSB_CASE(1) GSB_CASE(2) GSB_CASE(3) GSB_CASE(4) GSB_CASE(5) GSB_CASE(8)

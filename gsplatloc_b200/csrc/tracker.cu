@@ -40,6 +40,7 @@ struct gsb_tracker {
     int *counts = nullptr, *offsets = nullptr, *cursor = nullptr, *n_isects = nullptr, *overflow = nullptr;
     uint64_t* keys = nullptr;
     int* flatten_ids = nullptr;
+    unsigned char* masks = nullptr;   // per tile entry: which 8x4 patches it can reach (written by raster_fwd)
     int64_t cap = 0;
     float *ed = nullptr, *alpha = nullptr, *v_depth = nullptr, *v_alpha = nullptr;
     int* last_ids = nullptr;
@@ -88,7 +89,7 @@ static void enqueue_iteration(gsb_tracker* t, bool forward_only, cudaEvent_t* ma
     launch_tile_sort(C, t->n_tiles, t->tile_bits, t->offsets, t->keys, t->flatten_ids, nullptr, (int)t->cap, t->stop, st);
     GSB_MARK();
     launch_raster_fwd_packed(C, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->offsets, t->n_isects, t->flatten_ids,
-                             t->ed, t->alpha, t->last_ids, 1, t->stop, st);
+                             t->ed, t->alpha, t->last_ids, 1, t->stop, t->masks, st);
     GSB_MARK();
     if (forward_only) return;
     const float inv_p = 1.f / ((float)t->W * (float)t->H);
@@ -98,7 +99,7 @@ static void enqueue_iteration(gsb_tracker* t, bool forward_only, cudaEvent_t* ma
     GSB_MARK();
     launch_raster_bwd_lift(C, N, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->offsets, t->n_isects, t->flatten_ids,
                            t->alpha, t->last_ids, t->v_depth, t->v_alpha, t->means, t->quats, t->scales, t->viewmats,
-                           t->Ks, c.eps2d, t->partials, t->stop, st);
+                           t->Ks, c.eps2d, t->partials, t->stop, t->masks, st);
     GSB_MARK();
     launch_pose_finish(C, t->n_tiles, t->n_loss_blocks, t->partials, t->loss_partials, t->viewmats, t->state, t->stop,
                        c, inv_p, 1.f / (3.f * (float)t->H), t->history, t->history_cap, st);
@@ -123,9 +124,11 @@ static int ensure_capacity(gsb_tracker* t) {
         int64_t want = m + m / 4 + 65536;
         if (t->keys) cudaFree(t->keys);
         if (t->flatten_ids) cudaFree(t->flatten_ids);
-        t->keys = nullptr; t->flatten_ids = nullptr;
+        if (t->masks) cudaFree(t->masks);
+        t->keys = nullptr; t->flatten_ids = nullptr; t->masks = nullptr;
         TCK(cudaMalloc(&t->keys, sizeof(uint64_t) * (size_t)want), "alloc keys");
         TCK(cudaMalloc(&t->flatten_ids, sizeof(int) * (size_t)want), "alloc flatten_ids");
+        TCK(cudaMalloc(&t->masks, (size_t)want), "alloc masks");
         t->cap = want;
         invalidate_graph(t);
     }
@@ -218,7 +221,7 @@ void gsb_tracker_destroy(gsb_tracker* t) {
     cudaStreamSynchronize(t->stream);
     invalidate_graph(t);
     void* bufs[] = {t->means, t->quats, t->scales, t->opac, t->gt, t->Ks, t->viewmats, t->state, t->stop, t->rec,
-                    t->bbox, t->counts, t->offsets, t->cursor, t->n_isects, t->keys, t->flatten_ids, t->ed, t->alpha,
+                    t->bbox, t->counts, t->offsets, t->cursor, t->n_isects, t->keys, t->flatten_ids, t->masks, t->ed, t->alpha,
                     t->v_depth, t->v_alpha, t->last_ids, t->partials, t->loss_partials, t->normal_rows,
                     t->history};
     for (void* b : bufs)
