@@ -246,25 +246,35 @@ __device__ __forceinline__ void cex(uint64_t* a, int x, int y) {
     if (u > v) { a[x] = v; a[y] = u; }
 }
 
-__device__ void bitonic_sort(uint64_t* a, int n) {
-    int P = 1;
-    while (P < n) P <<= 1;
-    for (int h = 2; h <= P; h <<= 1) {
-        int half = h >> 1;
-        for (int t = threadIdx.x; t < (P >> 1); t += blockDim.x) {
-            int q = (t / half) * h, r = t % half;
-            int x = q + r, y = q + h - r - 1;
+// Rounds whose partner distance is <= 32 keep every pair inside the 64 consecutive elements a warp owns in that round
+// (thread t touches elements 2t - (t mod d) and its partner), so between two such rounds a __syncwarp is enough; a
+// block barrier is only needed when the round before or after reaches across warps.  Index arithmetic is shifts and
+// masks (all sizes are powers of two).  ``smem``: the array lives in shared memory (else global: block barriers only).
+__device__ __forceinline__ void sort_round_barrier(bool smem, int cur_d, int next_d) {
+    if (smem && cur_d <= 32 && next_d <= 32) __syncwarp(); else __syncthreads();
+}
+
+__device__ void bitonic_sort(uint64_t* a, int n, bool smem) {
+    int lgP = 0;
+    while ((1 << lgP) < n) ++lgP;
+    const int halfP = (1 << lgP) >> 1;
+    for (int lh = 1; lh <= lgP; ++lh) {          // h = 1 << lh
+        const int lhalf = lh - 1, half = 1 << lhalf;
+        const int next_stage_d = (lh < lgP) ? (1 << lh) : (1 << 30);   // the flip of the next stage (or the end)
+        for (int t = threadIdx.x; t < halfP; t += blockDim.x) {
+            const int r = t & (half - 1), q = (t >> lhalf) << lh;
+            const int x = q + r, y = q + (1 << lh) - r - 1;
             if (y < n) cex(a, x, y);
         }
-        __syncthreads();
-        for (int hh = half; hh >= 2; hh >>= 1) {
-            int hf = hh >> 1;
-            for (int t = threadIdx.x; t < (P >> 1); t += blockDim.x) {
-                int q = (t / hf) * hh, r = t % hf;
-                int x = q + r, y = x + hf;
+        sort_round_barrier(smem, half, lh >= 2 ? (half >> 1) : next_stage_d);
+        for (int lhf = lhalf - 1; lhf >= 0; --lhf) {
+            const int hf = 1 << lhf;
+            for (int t = threadIdx.x; t < halfP; t += blockDim.x) {
+                const int r = t & (hf - 1);
+                const int x = ((t >> lhf) << (lhf + 1)) + r, y = x + hf;
                 if (y < n) cex(a, x, y);
             }
-            __syncthreads();
+            sort_round_barrier(smem, hf, lhf > 0 ? (hf >> 1) : next_stage_d);
         }
     }
 }
@@ -287,7 +297,7 @@ __global__ void __launch_bounds__(256) tile_sort_kernel(int n_tiles, int tile_bi
         a = sk;
     }
     __syncthreads();
-    if (n > 1) bitonic_sort(a, n);
+    if (n > 1) bitonic_sort(a, n, n <= SORT_SMEM);
     int64_t hi = ((int64_t)cam << (32 + tile_bits)) | ((int64_t)(bin % n_tiles) << 32);
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
         uint64_t k = a[i];
