@@ -558,17 +558,23 @@ __global__ void __launch_bounds__(256, GSB_BWD_OCC) raster_bwd_quad_kernel(
     const int first = min(range_end - 1, warp_bin_final);
     int top = first;
     bool more = top >= range_start;
+    // (patch mask, Gaussian id) of the chunk about to be gathered are fetched one chunk ahead, so that the dependent
+    // record loads of a chunk are the only global-memory round trip left on the warp's critical path
+    unsigned nxt_m = 0u;
+    int nxt_g = 0;
+    if (top - lane >= range_start) { nxt_m = masks[top - lane]; nxt_g = flatten_ids[top - lane]; }
     while (more || r_tail - r_head > 0) {
         if (more) {
             // ---- gather 32 entries of the tile list (back to front), keep those that can reach this patch
+            // (the forward stored every staged entry's patch mask: non-reaching entries cost one byte load)
             const int pos = top - lane;
-            unsigned hit = 0u;
+            const unsigned hit = (pos >= range_start) ? ((nxt_m >> wid) & 1u) : 0u;
+            const int g = nxt_g;
+            top -= 32;
+            more = top >= range_start;
+            if (top - lane >= range_start) { nxt_m = masks[top - lane]; nxt_g = flatten_ids[top - lane]; }
             float4 e0, e1;
-            int g = 0;
-            // the forward stored every staged entry's patch mask: non-reaching entries cost one byte load here
-            if (pos >= range_start) hit = ((unsigned)masks[pos] >> wid) & 1u;
             if (hit) {
-                g = flatten_ids[pos];
                 const float4 r0 = __ldg(rec + 2 * (size_t)g), r1 = __ldg(rec + 2 * (size_t)g + 1);
                 e0 = make_float4(r0.x, r0.y, 0.5f * GSB_NEG_LOG2E * r1.x, GSB_NEG_LOG2E * r1.y);
                 e1 = make_float4(0.5f * GSB_NEG_LOG2E * r1.z, r0.w, r0.z, __int_as_float(pos));
@@ -579,8 +585,6 @@ __global__ void __launch_bounds__(256, GSB_BWD_OCC) raster_bwd_quad_kernel(
                 ws.rec[slot][0] = e0; ws.rec[slot][1] = e1; ws.gid[slot] = g;
             }
             r_tail += __popc(bits);
-            top -= 32;
-            more = top >= range_start;
             __syncwarp();
         }
         // ---- consume steps of eight compacted entries (a partial last step is padded with dead entries)
