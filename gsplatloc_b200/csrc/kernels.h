@@ -61,7 +61,8 @@ void launch_raster_bwd_lift(int C, int N, int W, int H, int tile_w, int tile_h, 
                             const float* render_alphas, const int* last_ids, const float* v_depth,
                             const float* v_alpha, const float* means, const float* quats, const float* scales,
                             const float* viewmats, const float* Ks, float eps2d, float* partials, const int* stop,
-                            const unsigned char* masks, cudaStream_t st);
+                            const unsigned char* masks, const int* iso_flag, cudaStream_t st);
+void launch_map_iso(int N, const float* scales, int* flag, cudaStream_t st);
 int launch_raster_bwd_soa(int cdim, int C, int N, int W, int H, int tile_w, int tile_h, const float* means2d,
                           const float* conics, const float* colors, const float* opacities, const float* backgrounds,
                           const int* tile_offsets, int n_isects, const int* flatten_ids, const float* render_alphas,

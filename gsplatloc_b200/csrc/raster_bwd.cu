@@ -1,14 +1,7 @@
 // Back-to-front replay of the compositing and its VJP (Appendix A.5 / A.6).
-//
-// One 256-thread block per (camera, 16x16 tile); each warp owns an 8x4 pixel patch and walks only the staged
-// Gaussians whose 8-bit patch mask (common.cuh) says their alpha >= 1/255 ellipse can reach that patch.  For every
-// such Gaussian the per-pixel gradient terms (v_xy[2], v_conic[3], v_colour[CDIM], v_opacity) are summed over the warp with a
-// halving butterfly (log2 steps, 9 shuffles for 8 values instead of 40).
-//   LIFT = true (tracker): the warp sums land in a per-warp slot of shared memory (no atomics, fixed order =
-//       deterministic); after each batch one thread per Gaussian adds the 8 warp slots and pushes the 6 numbers
-//       straight through the projection Jacobian (A.6) into a 12-float d(loss)/d(viewmat[:3,:4]) accumulator. The
-//       block writes ONE 12-float partial per tile; no per-Gaussian gradient ever reaches HBM.
-//   LIFT = false (op-level twin of gsplat rasterize_to_pixels_bwd): warp sums go to global atomics.
+//   raster_bwd_kernel<CDIM>  : op-level twin of gsplat rasterize_to_pixels_bwd (per-Gaussian gradients by atomics).
+//   raster_bwd_quad_kernel   : tracker path, ED only; per-Gaussian sums never reach HBM: they are lifted through the
+//                              projection Jacobian (A.6) into ONE 12-float d(loss)/d(viewmat[:3,:4]) partial per tile.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -86,55 +79,67 @@ struct LiftCtx {
     const float* scales;
     int W, H, N, cam_index;
     float eps2d;
+    int iso;   // every Gaussian has sx == sy == sz: Sigma = s^2 I whatever the quaternion (tracker.cu map_iso_kernel)
 };
 
-// A.6 for one staged Gaussian: the six tile-summed numbers (v_xy, v_conic, v_depth) -> 12 pose-gradient numbers,
-// accumulated into this thread's column of s_pose[12][BWD_BATCH].  Out of line on purpose: the camera, the
-// re-projection temporaries and the accumulators must not compete for registers with the replay loop.
+// A.6 for one Gaussian: the six patch-summed numbers (v_xy, v_conic, v_depth) -> 12 pose-gradient numbers, accumulated
+// into this thread's column pose_col[k * col_stride].  Out of line on purpose: the camera, the re-projection
+// temporaries and the accumulators must not compete for registers with the replay loop.
+// Isotropic maps (GsplatLoc's: scales = one KNN distance repeated three times, geometry.py:44-66) take a short cut:
+// Sigma = Rq diag(s,s,s)^2 Rq^T = s^2 I for ANY quaternion and Sigma_cam = R Sigma R^T = s^2 I, so the quaternion
+// and the two 3x3 congruences drop out (the literal zeros below fold away after inlining).
 __device__ __noinline__ void lift_to_pose(const LiftCtx* __restrict__ ctx, int flat_id, float g0, float g1, float g2,
                                           float g3, float g4, float g5, float* __restrict__ pose_col,
                                           int col_stride) {
     const Cam camera = ctx->cam;
     const int n = flat_id - ctx->cam_index * ctx->N;
     const float mean[3] = {__ldg(ctx->means + n * 3), __ldg(ctx->means + n * 3 + 1), __ldg(ctx->means + n * 3 + 2)};
-    const float4 q4 = __ldg(reinterpret_cast<const float4*>(ctx->quats) + n);
-    const float q[4] = {q4.x, q4.y, q4.z, q4.w};
-    const float sc[3] = {__ldg(ctx->scales + n * 3), __ldg(ctx->scales + n * 3 + 1), __ldg(ctx->scales + n * 3 + 2)};
-    Proj p; float S[6], Sc[6];
-    project_gaussian(camera, mean, q, sc, ctx->W, ctx->H, ctx->eps2d, -1e30f, 1e30f, -1.f, p, S, Sc);
     float v_pc[3], vS[6], acc[12];
 #pragma unroll
     for (int k = 0; k < 12; ++k) acc[k] = 0.f;
-    project_vjp(camera, p, Sc, g0, g1, g2, g3, g4, g5, v_pc, vS);
-    pose_accumulate(camera, mean, S, v_pc, vS, acc, acc + 9);
+    if (ctx->iso) {
+        const float sc = __ldg(ctx->scales + n * 3);
+        const float s2 = sc * sc;
+        const float S[6] = {s2, 0.f, 0.f, s2, 0.f, s2};
+        Proj p;
+        p.px = camera.R[0] * mean[0] + camera.R[1] * mean[1] + camera.R[2] * mean[2] + camera.t[0];
+        p.py = camera.R[3] * mean[0] + camera.R[4] * mean[1] + camera.R[5] * mean[2] + camera.t[1];
+        p.pz = camera.R[6] * mean[0] + camera.R[7] * mean[1] + camera.R[8] * mean[2] + camera.t[2];
+        persp_project(camera, S, ctx->W, ctx->H, ctx->eps2d, -1.f, p);
+        project_vjp(camera, p, S, g0, g1, g2, g3, g4, g5, v_pc, vS);
+        pose_accumulate(camera, mean, S, v_pc, vS, acc, acc + 9);
+    } else {
+        const float4 q4 = __ldg(reinterpret_cast<const float4*>(ctx->quats) + n);
+        const float q[4] = {q4.x, q4.y, q4.z, q4.w};
+        const float sc[3] = {__ldg(ctx->scales + n * 3), __ldg(ctx->scales + n * 3 + 1), __ldg(ctx->scales + n * 3 + 2)};
+        Proj p; float S[6], Sc[6];
+        project_gaussian(camera, mean, q, sc, ctx->W, ctx->H, ctx->eps2d, -1e30f, 1e30f, -1.f, p, S, Sc);
+        project_vjp(camera, p, Sc, g0, g1, g2, g3, g4, g5, v_pc, vS);
+        pose_accumulate(camera, mean, S, v_pc, vS, acc, acc + 9);
+    }
 #pragma unroll
     for (int k = 0; k < 12; ++k) pose_col[k * col_stride] += acc[k];
 }
 
-template <int CDIM, bool PACKED, bool LIFT>
-__global__ void __launch_bounds__(256, LIFT ? 4 : 2) raster_bwd_kernel(
-    int C, int N, int W, int H, int tile_w, int tile_h, const float4* __restrict__ rec,
-    const float* __restrict__ means2d, const float* __restrict__ conics, const float* __restrict__ colors,
-    const float* __restrict__ opacities, const float* __restrict__ backgrounds,
-    const int* __restrict__ tile_offsets, const int* __restrict__ n_isects_dev, int n_isects_host,
+// Op-level twin of gsplat rasterize_to_pixels_bwd (SoA inputs, CDIM colour channels): block-cooperative staging,
+// pixel per lane, warp sums by the halving butterfly, one global atomicAdd per warp per Gaussian per quantity.
+template <int CDIM>
+__global__ void __launch_bounds__(256, 2) raster_bwd_kernel(
+    int C, int N, int W, int H, int tile_w, int tile_h, const float* __restrict__ means2d,
+    const float* __restrict__ conics, const float* __restrict__ colors, const float* __restrict__ opacities,
+    const float* __restrict__ backgrounds, const int* __restrict__ tile_offsets, int n_isects,
     const int* __restrict__ flatten_ids, const float* __restrict__ render_alphas, const int* __restrict__ last_ids,
     const float* __restrict__ v_render_colors, const float* __restrict__ v_render_alphas,
     float* __restrict__ v_means2d, float* __restrict__ v_conics, float* __restrict__ v_colors,
-    float* __restrict__ v_opacities, const float* __restrict__ means, const float* __restrict__ quats,
-    const float* __restrict__ scales, const float* __restrict__ viewmats, const float* __restrict__ Ks, float eps2d,
-    float* __restrict__ partials, const int* __restrict__ stop) {
+    float* __restrict__ v_opacities) {
     constexpr int RS = BwdCfg<CDIM>::RS;
     constexpr int NV = BwdCfg<CDIM>::NV;
     __shared__ __align__(16) float sm[BWD_BATCH * RS];
     __shared__ int s_id[BWD_BATCH];
-    __shared__ __align__(16) float s_acc[LIFT ? 8 * BWD_BATCH * 6 : 4];
-    __shared__ float s_pose[LIFT ? 12 * BWD_BATCH : 1];
-    __shared__ LiftCtx s_ctx;
     __shared__ int s_max[8];
     __shared__ unsigned char s_mask[BWD_BATCH];
 
     const int cam = blockIdx.z;
-    if (stop && stop[cam]) return;
     const int tile_id = blockIdx.y * tile_w + blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int j = blockIdx.x * 16 + (wid & 1) * 8 + (lane & 7);
@@ -143,19 +148,9 @@ __global__ void __launch_bounds__(256, LIFT ? 4 : 2) raster_bwd_kernel(
     const float tile_x0 = (float)(blockIdx.x * 16), tile_y0 = (float)(blockIdx.y * 16);
     const bool inside = (i < H) && (j < W);
     const size_t pix = ((size_t)cam * H + min(i, H - 1)) * W + min(j, W - 1);
-    const int n_isects = n_isects_dev ? *n_isects_dev : n_isects_host;
     const int bin = cam * tile_w * tile_h + tile_id;
     const int range_start = tile_offsets[bin];
     const int range_end = (bin == C * tile_w * tile_h - 1) ? n_isects : tile_offsets[bin + 1];
-
-    if (LIFT) {
-        if (tid == 0) {
-            s_ctx.cam = load_cam(viewmats + cam * 16, Ks + cam * 9);
-            s_ctx.means = means; s_ctx.quats = quats; s_ctx.scales = scales;
-            s_ctx.W = W; s_ctx.H = H; s_ctx.N = N; s_ctx.cam_index = cam; s_ctx.eps2d = eps2d;
-        }
-        for (int q = tid; q < 12 * BWD_BATCH; q += 256) s_pose[q] = 0.f;
-    }
 
     const float T_final = inside ? 1.f - render_alphas[pix] : 1.f;
     float T = T_final;
@@ -181,12 +176,10 @@ __global__ void __launch_bounds__(256, LIFT ? 4 : 2) raster_bwd_kernel(
 #pragma unroll
     for (int w = 1; w < 8; ++w) block_bin_final = max(block_bin_final, s_max[w]);
 
-    // which of the reduced values this lane ends up holding (see warp_reduce_multi) and where it stores it
+    // which of the reduced values this lane ends up holding (see warp_reduce_multi)
     const int ridx = (NV == 8) ? ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1)
                                : ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
     const bool holder = (NV == 8) ? ((lane & 3) == 0) : ((lane & 1) == 0);
-    float* const acc_slot = s_acc + (LIFT ? wid * BWD_BATCH * 6 + ridx : 0);
-    const bool acc_writer = holder && ridx < 6;
 
     // positions > block_bin_final were composited by no pixel of this tile: start the replay there
     const int first = min(range_end - 1, block_bin_final);
@@ -202,28 +195,17 @@ __global__ void __launch_bounds__(256, LIFT ? 4 : 2) raster_bwd_kernel(
                 const int g = flatten_ids[batch_end - tid];
                 s_id[tid] = g;
                 float* dst = sm + tid * RS;
-                if (PACKED) {
-                    const float4 r0 = __ldg(rec + 2 * (size_t)g), r1 = __ldg(rec + 2 * (size_t)g + 1);
-                    reinterpret_cast<float4*>(dst)[0] = make_float4(r0.x, r0.y, r1.x, r1.y);
-                    reinterpret_cast<float4*>(dst)[1] = make_float4(r1.z, r0.w, r0.z, 0.f);
-                    m = patch_mask(r0.x, r0.y, r1.x, r1.y, r1.z, r0.w, tile_x0, tile_y0);
-                } else {
-                    const float2 xy = reinterpret_cast<const float2*>(means2d)[g];
-                    const float ca = conics[3 * (size_t)g], cb = conics[3 * (size_t)g + 1], cc = conics[3 * (size_t)g + 2];
-                    const float o = opacities[g];
-                    reinterpret_cast<float4*>(dst)[0] = make_float4(xy.x, xy.y, ca, cb);
-                    dst[4] = cc;
-                    dst[5] = o;
+                const float2 xy = reinterpret_cast<const float2*>(means2d)[g];
+                const float ca = conics[3 * (size_t)g], cb = conics[3 * (size_t)g + 1], cc = conics[3 * (size_t)g + 2];
+                const float o = opacities[g];
+                reinterpret_cast<float4*>(dst)[0] = make_float4(xy.x, xy.y, ca, cb);
+                dst[4] = cc;
+                dst[5] = o;
 #pragma unroll
-                    for (int k = 0; k < CDIM; ++k) dst[6 + k] = colors[(size_t)g * CDIM + k];
-                    m = patch_mask(xy.x, xy.y, ca, cb, cc, o, tile_x0, tile_y0);
-                }
+                for (int k = 0; k < CDIM; ++k) dst[6 + k] = colors[(size_t)g * CDIM + k];
+                m = patch_mask(xy.x, xy.y, ca, cb, cc, o, tile_x0, tile_y0);
             }
             s_mask[tid] = (unsigned char)m;
-        }
-        if (LIFT) {
-            float4* z = reinterpret_cast<float4*>(s_acc);
-            for (int q = tid; q < 8 * BWD_BATCH * 6 / 4; q += 256) z[q] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         __syncthreads();
 
@@ -244,8 +226,7 @@ __global__ void __launch_bounds__(256, LIFT ? 4 : 2) raster_bwd_kernel(
                 const float alpha = fminf(GSB_ALPHA_MAX, opac * vis);
                 const bool valid = inside && (t >= my_first) && !(sigma < 0.f || alpha < GSB_ALPHA_MIN);
                 if (!__any_sync(0xffffffffu, valid)) continue;
-                // v[]: 0,1 = v_xy; 2,3,4 = v_conic; 5 = v_opacity (generic) ; 6.. = v_colour
-                //      LIFT: 5 = v_colour (depth) and v_opacity is not needed
+                // v[]: 0,1 = v_xy; 2,3,4 = v_conic; 5 = v_opacity; 6.. = v_colour
                 float v[NV];
 #pragma unroll
                 for (int k = 0; k < NV; ++k) v[k] = 0.f;
@@ -261,7 +242,7 @@ __global__ void __launch_bounds__(256, LIFT ? 4 : 2) raster_bwd_kernel(
                     float v_alpha = 0.f;
 #pragma unroll
                     for (int k = 0; k < CDIM; ++k) {
-                        v[(LIFT ? 5 : 6) + k] = fac * v_rc[k];
+                        v[6 + k] = fac * v_rc[k];
                         v_alpha += (col[k] * T - buffer[k] * ra) * v_rc[k];
                     }
                     v_alpha += v_ra_T * ra;
@@ -272,15 +253,13 @@ __global__ void __launch_bounds__(256, LIFT ? 4 : 2) raster_bwd_kernel(
                         v[4] = 0.5f * v_sigma * dy * dy;
                         v[0] = v_sigma * (p0.z * dx + p0.w * dy);
                         v[1] = v_sigma * (p0.w * dx + p1.x * dy);
-                        if (!LIFT) v[5] = vis * v_alpha;
+                        v[5] = vis * v_alpha;
                     }
 #pragma unroll
                     for (int k = 0; k < CDIM; ++k) buffer[k] += col[k] * fac;
                 }
                 warp_reduce_multi<NV>(v, lane);
-                if (LIFT) {
-                    if (acc_writer) acc_slot[t * 6] = v[0];
-                } else if (holder && ridx < 6 + CDIM) {
+                if (holder && ridx < 6 + CDIM) {
                     const size_t g = (size_t)s_id[t];
                     float* dst = ridx < 2 ? v_means2d + 2 * g + ridx
                                : ridx < 5 ? v_conics + 3 * g + (ridx - 2)
@@ -289,190 +268,13 @@ __global__ void __launch_bounds__(256, LIFT ? 4 : 2) raster_bwd_kernel(
                 }
             }
         }
-
-        if (LIFT) {
-            __syncthreads();
-            if (tid < batch_size) {
-                float gsum[6];
-#pragma unroll
-                for (int k = 0; k < 6; ++k) gsum[k] = 0.f;
-#pragma unroll
-                for (int w = 0; w < 8; ++w) {
-                    const float2* src = reinterpret_cast<const float2*>(s_acc + (w * BWD_BATCH + tid) * 6);
-                    float2 a = src[0], bq = src[1], cq = src[2];
-                    gsum[0] += a.x; gsum[1] += a.y; gsum[2] += bq.x; gsum[3] += bq.y; gsum[4] += cq.x; gsum[5] += cq.y;
-                }
-                bool any = false;
-#pragma unroll
-                for (int k = 0; k < 6; ++k) any |= (gsum[k] != 0.f);
-                if (any) lift_to_pose(&s_ctx, s_id[tid], gsum[0], gsum[1], gsum[2], gsum[3], gsum[4], gsum[5], s_pose + tid,
-                                      BWD_BATCH);
-            }
-        }
-    }
-
-    if (LIFT) {
-        __syncthreads();
-        // 12 numbers x BWD_BATCH thread columns -> one 12-float partial of this tile (fixed order: deterministic)
-        for (int k = wid; k < 12; k += 8) {
-            float s = 0.f;
-#pragma unroll
-            for (int q = 0; q < BWD_BATCH / 32; ++q) s += s_pose[k * BWD_BATCH + q * 32 + lane];
-            s = warp_sum(s);
-            if (lane == 0) partials[(size_t)bin * 12 + k] = s;
-        }
     }
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// Tracker path, second generation: every warp is an independent unit (no __syncthreads in the replay).
+// Tracker path: "quad-scan" replay, every warp an independent unit (no __syncthreads until the final reduction).
 //
-// The block-cooperative kernel above spends ~40 % of its stall samples at the barrier that closes each staged batch
-// (profiles/r1_c_iteration_full.md): the eight 8x4 patches of a tile finish their share of a batch at different times
-// and everybody waits for the slowest.  Here a warp walks the tile's sorted list on its own, back to front from ITS
-// last composited entry, 32 entries at a time: lane l gathers entry l, tests it against the warp's patch
-// (patch_mask), a ballot gives the entries to replay, each replayed entry is read back from a 1 KB per-warp staging
-// area.  The six per-Gaussian sums leave the butterfly reduction into a per-warp queue; when 32 are queued every lane
-// lifts one of them through the projection Jacobian (A.6) into its own 12 pose accumulators.  The lift is linear in
-// the six sums, so lifting per-warp partial sums is exact; it costs more lifts (one per (patch, Gaussian) instead of
-// one per (tile, Gaussian)) but no barrier, no zeroing of slot arrays and no cross-warp summation.  Order of every
-// floating-point sum is fixed -> deterministic, as before.  One partial (12 floats) per tile leaves the block.
-struct WarpScratch {
-    float4 rec[32][2];   // staged entries {x, y, a, b}, {c, opacity, depth, -}
-    int gid[32];         // their flat Gaussian ids
-    float qsum[64][6];   // lift queue (ring of 64): v_xy[2], v_conic[3], v_depth
-    int qid[64];
-};
-
-__global__ void __launch_bounds__(256, 4) raster_bwd_warp_kernel(
-    int C, int N, int W, int H, int tile_w, int tile_h, const float4* __restrict__ rec,
-    const int* __restrict__ tile_offsets, const int* __restrict__ n_isects_dev, const int* __restrict__ flatten_ids,
-    const float* __restrict__ render_alphas, const int* __restrict__ last_ids, const float* __restrict__ v_depth,
-    const float* __restrict__ v_alpha_img, const float* __restrict__ means, const float* __restrict__ quats,
-    const float* __restrict__ scales, const float* __restrict__ viewmats, const float* __restrict__ Ks, float eps2d,
-    float* __restrict__ partials, const int* __restrict__ stop) {
-    __shared__ WarpScratch s_w[8];
-    __shared__ float s_pose[12 * 256];
-    __shared__ LiftCtx s_ctx;
-
-    const int cam = blockIdx.z;
-    if (stop && stop[cam]) return;
-    const int tile_id = blockIdx.y * tile_w + blockIdx.x;
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int j = blockIdx.x * 16 + (wid & 1) * 8 + (lane & 7);
-    const int i = blockIdx.y * 16 + (wid >> 1) * 4 + (lane >> 3);
-    const float px = (float)j + 0.5f, py = (float)i + 0.5f;
-    const float tile_x0 = (float)(blockIdx.x * 16), tile_y0 = (float)(blockIdx.y * 16);
-    const bool inside = (i < H) && (j < W);
-    const size_t pix = ((size_t)cam * H + min(i, H - 1)) * W + min(j, W - 1);
-    const int bin = cam * tile_w * tile_h + tile_id;
-    const int range_start = tile_offsets[bin];
-    const int range_end = (bin == C * tile_w * tile_h - 1) ? *n_isects_dev : tile_offsets[bin + 1];
-
-    if (tid == 0) {
-        s_ctx.cam = load_cam(viewmats + cam * 16, Ks + cam * 9);
-        s_ctx.means = means; s_ctx.quats = quats; s_ctx.scales = scales;
-        s_ctx.W = W; s_ctx.H = H; s_ctx.N = N; s_ctx.cam_index = cam; s_ctx.eps2d = eps2d;
-    }
-#pragma unroll
-    for (int k = 0; k < 12; ++k) s_pose[k * 256 + tid] = 0.f;
-    __syncthreads();
-
-    const float T_final = inside ? 1.f - render_alphas[pix] : 1.f;
-    float T = T_final, buffer = 0.f;
-    const float v_rc = inside ? v_depth[pix] : 0.f;
-    const float v_ra_T = inside ? T_final * v_alpha_img[pix] : 0.f;
-    const int bin_final = inside ? last_ids[pix] : -1;
-    int warp_bin_final = bin_final;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) warp_bin_final = max(warp_bin_final, __shfl_xor_sync(0xffffffffu, warp_bin_final, o));
-
-    WarpScratch& ws = s_w[wid];
-    const int ridx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);   // see warp_reduce_multi<8>
-    const bool q_writer = ((lane & 3) == 0) && ridx < 6;
-    float* const pose_col = s_pose + tid;
-    int q_head = 0, q_tail = 0;   // ring indices (uniform across the warp)
-
-    // entries behind the warp's last composited one were composited by none of its pixels
-    const int first = min(range_end - 1, warp_bin_final);
-    for (int top = first; top >= range_start; top -= 32) {
-        const int pos = top - lane;
-        unsigned hit = 0u;
-        if (pos >= range_start) {
-            const int g = flatten_ids[pos];
-            const float4 r0 = __ldg(rec + 2 * (size_t)g), r1 = __ldg(rec + 2 * (size_t)g + 1);
-            ws.rec[lane][0] = make_float4(r0.x, r0.y, r1.x, r1.y);
-            ws.rec[lane][1] = make_float4(r1.z, r0.w, r0.z, 0.f);
-            ws.gid[lane] = g;
-            hit = (patch_mask(r0.x, r0.y, r1.x, r1.y, r1.z, r0.w, tile_x0, tile_y0) >> wid) & 1u;
-        }
-        unsigned bits = __ballot_sync(0xffffffffu, hit);
-        __syncwarp();
-        while (bits) {
-            const int t = __ffs(bits) - 1;
-            bits &= bits - 1;
-            const float4 p0 = ws.rec[t][0], p1 = ws.rec[t][1];
-            const float opac = p1.y;
-            const float dx = p0.x - px, dy = p0.y - py;
-            const float sigma = 0.5f * (p0.z * dx * dx + p1.x * dy * dy) + p0.w * dx * dy;
-            const float vis = exp_neg_fast(sigma);
-            const float alpha = fminf(GSB_ALPHA_MAX, opac * vis);
-            const bool valid = (top - t <= bin_final) && !(sigma < 0.f || alpha < GSB_ALPHA_MIN);
-            if (!__any_sync(0xffffffffu, valid)) continue;
-            float v[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) v[k] = 0.f;
-            if (valid) {
-                const float ra = rcp_fast(1.f - alpha);   // 1 - alpha >= 1e-3
-                T *= ra;
-                const float fac = alpha * T;
-                v[5] = fac * v_rc;
-                const float v_al = (p1.z * T - buffer * ra) * v_rc + v_ra_T * ra;
-                if (opac * vis <= GSB_ALPHA_MAX) {
-                    const float v_sigma = -opac * vis * v_al;
-                    v[2] = 0.5f * v_sigma * dx * dx;
-                    v[3] = v_sigma * dx * dy;
-                    v[4] = 0.5f * v_sigma * dy * dy;
-                    v[0] = v_sigma * (p0.z * dx + p0.w * dy);
-                    v[1] = v_sigma * (p0.w * dx + p1.x * dy);
-                }
-                buffer += p1.z * fac;
-            }
-            warp_reduce_multi<8>(v, lane);
-            const int slot = q_tail & 63;
-            if (q_writer) ws.qsum[slot][ridx] = v[0];
-            if (lane == 0) ws.qid[slot] = ws.gid[t];
-            ++q_tail;
-        }
-        __syncwarp();   // queue entries visible; staging area is rewritten by the next chunk
-        if (q_tail - q_head >= 32) {   // a chunk adds at most 32 entries: the ring of 64 never overflows
-            const int slot = (q_head + lane) & 63;
-            lift_to_pose(&s_ctx, ws.qid[slot], ws.qsum[slot][0], ws.qsum[slot][1], ws.qsum[slot][2], ws.qsum[slot][3],
-                         ws.qsum[slot][4], ws.qsum[slot][5], pose_col, 256);
-            q_head += 32;
-        }
-    }
-    __syncwarp();
-    if (lane < q_tail - q_head) {
-        const int slot = (q_head + lane) & 63;
-        lift_to_pose(&s_ctx, ws.qid[slot], ws.qsum[slot][0], ws.qsum[slot][1], ws.qsum[slot][2], ws.qsum[slot][3],
-                     ws.qsum[slot][4], ws.qsum[slot][5], pose_col, 256);
-    }
-    __syncthreads();
-    // 12 numbers x 256 thread columns -> one 12-float partial of this tile (fixed order: deterministic)
-    for (int k = wid; k < 12; k += 8) {
-        float s = 0.f;
-#pragma unroll
-        for (int q = 0; q < 8; ++q) s += s_pose[k * 256 + q * 32 + lane];
-        s = warp_sum(s);
-        if (lane == 0) partials[(size_t)bin * 12 + k] = s;
-    }
-}
-
-// ------------------------------------------------------------------------------------------------------------------
-// Tracker path, third generation: "quad-scan" replay.
-//
-// The pixel-per-lane replay above spends a third of its instructions on the 32-lane butterfly that sums six numbers
+// A pixel-per-lane replay (the op-level kernel above) spends a third of its instructions on the 32-lane butterfly that sums six numbers
 // per Gaussian, and evaluates one (pixel, Gaussian) pair per lane per ~120 warp instructions.  Here the warp's 8x4
 // patch is re-mapped: lane L = (column pr = L >> 2, Gaussian pair gq = L & 3) owns the FOUR pixels of column pr and
 // TWO of the eight Gaussians of a step, i.e. 8 pairs per lane per step with all Gaussian data in registers.
@@ -502,7 +304,8 @@ __global__ void __launch_bounds__(256, GSB_BWD_OCC) raster_bwd_quad_kernel(
     const float* __restrict__ render_alphas, const int* __restrict__ last_ids, const float* __restrict__ v_depth,
     const float* __restrict__ v_alpha_img, const float* __restrict__ means, const float* __restrict__ quats,
     const float* __restrict__ scales, const float* __restrict__ viewmats, const float* __restrict__ Ks, float eps2d,
-    float* __restrict__ partials, const int* __restrict__ stop, const unsigned char* __restrict__ masks) {
+    float* __restrict__ partials, const int* __restrict__ stop, const unsigned char* __restrict__ masks,
+    const int* __restrict__ iso_flag) {
     __shared__ QuadScratch s_w[8];
     __shared__ float s_pose[12 * 256];
     __shared__ LiftCtx s_ctx;
@@ -524,6 +327,7 @@ __global__ void __launch_bounds__(256, GSB_BWD_OCC) raster_bwd_quad_kernel(
         s_ctx.cam = load_cam(viewmats + cam * 16, Ks + cam * 9);
         s_ctx.means = means; s_ctx.quats = quats; s_ctx.scales = scales;
         s_ctx.W = W; s_ctx.H = H; s_ctx.N = N; s_ctx.cam_index = cam; s_ctx.eps2d = eps2d;
+        s_ctx.iso = iso_flag ? *iso_flag : 0;
     }
 #pragma unroll
     for (int k = 0; k < 12; ++k) s_pose[k * 256 + tid] = 0.f;
@@ -713,12 +517,12 @@ void launch_raster_bwd_lift(int C, int N, int W, int H, int tile_w, int tile_h, 
                             const float* render_alphas, const int* last_ids, const float* v_depth,
                             const float* v_alpha, const float* means, const float* quats, const float* scales,
                             const float* viewmats, const float* Ks, float eps2d, float* partials, const int* stop,
-                            const unsigned char* masks, cudaStream_t st) {
+                            const unsigned char* masks, const int* iso_flag, cudaStream_t st) {
     if (C * tile_w * tile_h == 0) return;
     dim3 grid(tile_w, tile_h, C);
     raster_bwd_quad_kernel<<<grid, 256, 0, st>>>(C, N, W, H, tile_w, tile_h, rec, tile_offsets, n_isects_dev,
                                                  flatten_ids, render_alphas, last_ids, v_depth, v_alpha, means, quats,
-                                                 scales, viewmats, Ks, eps2d, partials, stop, masks);
+                                                 scales, viewmats, Ks, eps2d, partials, stop, masks, iso_flag);
 }
 
 int launch_raster_bwd_soa(int cdim, int C, int N, int W, int H, int tile_w, int tile_h, const float* means2d,
@@ -730,16 +534,30 @@ int launch_raster_bwd_soa(int cdim, int C, int N, int W, int H, int tile_w, int 
     dim3 grid(tile_w, tile_h, C);
 #define GSB_CASE(D)                                                                                                 \
     case D:                                                                                                         \
-        raster_bwd_kernel<D, false, false><<<grid, 256, 0, st>>>(                                                   \
-            C, N, W, H, tile_w, tile_h, nullptr, means2d, conics, colors, opacities, backgrounds, tile_offsets,     \
-            nullptr, n_isects, flatten_ids, render_alphas, last_ids, v_render_colors, v_render_alphas, v_means2d,   \
-            v_conics, v_colors, v_opacities, nullptr, nullptr, nullptr, nullptr, nullptr, 0.f, nullptr, nullptr);   \
+        raster_bwd_kernel<D><<<grid, 256, 0, st>>>(C, N, W, H, tile_w, tile_h, means2d, conics, colors, opacities,       \
+                                                   backgrounds, tile_offsets, n_isects, flatten_ids, render_alphas, \
+                                                   last_ids, v_render_colors, v_render_alphas, v_means2d, v_conics, \
+                                                   v_colors, v_opacities);                                          \
         return 0;
     switch (cdim) {
         GSB_CASE(1) GSB_CASE(2) GSB_CASE(3) GSB_CASE(4) GSB_CASE(5) GSB_CASE(8)
         default: return -1;
     }
 #undef GSB_CASE
+}
+
+// *flag = 1 iff every Gaussian has three identical scales (then Sigma = s^2 I for any quaternion)
+__global__ void map_iso_init_kernel(int* __restrict__ flag) { *flag = 1; }
+__global__ void map_iso_kernel(int N, const float* __restrict__ scales, int* __restrict__ flag) {
+    int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    const float a = scales[n * 3], b = scales[n * 3 + 1], c = scales[n * 3 + 2];
+    if (!(a == b && b == c)) *flag = 0;
+}
+
+void launch_map_iso(int N, const float* scales, int* flag, cudaStream_t st) {
+    map_iso_init_kernel<<<1, 1, 0, st>>>(flag);
+    if (N > 0) map_iso_kernel<<<(N + 255) / 256, 256, 0, st>>>(N, scales, flag);
 }
 
 }  // namespace gsb

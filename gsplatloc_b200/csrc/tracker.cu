@@ -38,6 +38,7 @@ struct gsb_tracker {
     float4* rec = nullptr;
     uint2* bbox = nullptr;
     int *counts = nullptr, *offsets = nullptr, *cursor = nullptr, *n_isects = nullptr, *overflow = nullptr;
+    int* iso_flag = nullptr;   // 1 when the map is isotropic (n_isects + 2)
     uint64_t* keys = nullptr;
     int* flatten_ids = nullptr;
     unsigned char* masks = nullptr;   // per tile entry: which 8x4 patches it can reach (written by raster_fwd)
@@ -99,7 +100,7 @@ static void enqueue_iteration(gsb_tracker* t, bool forward_only, cudaEvent_t* ma
     GSB_MARK();
     launch_raster_bwd_lift(C, N, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->offsets, t->n_isects, t->flatten_ids,
                            t->alpha, t->last_ids, t->v_depth, t->v_alpha, t->means, t->quats, t->scales, t->viewmats,
-                           t->Ks, c.eps2d, t->partials, t->stop, t->masks, st);
+                           t->Ks, c.eps2d, t->partials, t->stop, t->masks, t->iso_flag, st);
     GSB_MARK();
     launch_pose_finish(C, t->n_tiles, t->n_loss_blocks, t->partials, t->loss_partials, t->viewmats, t->state, t->stop,
                        c, inv_p, 1.f / (3.f * (float)t->H), t->history, t->history_cap, st);
@@ -194,8 +195,9 @@ int gsb_tracker_create(gsb_tracker** out, int C, int W, int H, void* stream) {
     TCK(cudaMalloc(&t->counts, sizeof(int) * nb), "alloc");
     TCK(cudaMalloc(&t->offsets, sizeof(int) * (nb + 1)), "alloc");
     TCK(cudaMalloc(&t->cursor, sizeof(int) * nb), "alloc");
-    TCK(cudaMalloc(&t->n_isects, sizeof(int) * 2), "alloc");
+    TCK(cudaMalloc(&t->n_isects, sizeof(int) * 3), "alloc");
     t->overflow = t->n_isects + 1;
+    t->iso_flag = t->n_isects + 2;
     TCK(cudaMalloc(&t->ed, sizeof(float) * P), "alloc");
     TCK(cudaMalloc(&t->alpha, sizeof(float) * P), "alloc");
     TCK(cudaMalloc(&t->v_depth, sizeof(float) * P), "alloc");
@@ -208,7 +210,7 @@ int gsb_tracker_create(gsb_tracker** out, int C, int W, int H, void* stream) {
     TCK(cudaMallocHost(&t->h_flags, sizeof(int) * (C + 2)), "alloc pinned");
     TCK(cudaMemsetAsync(t->counts, 0, sizeof(int) * nb, t->stream), "memset");
     TCK(cudaMemsetAsync(t->stop, 0, sizeof(int) * C, t->stream), "memset");
-    TCK(cudaMemsetAsync(t->n_isects, 0, sizeof(int) * 2, t->stream), "memset");
+    TCK(cudaMemsetAsync(t->n_isects, 0, sizeof(int) * 3, t->stream), "memset");
     TCK(cudaMemsetAsync(t->partials, 0, sizeof(float) * nb * 12, t->stream), "memset");
     TCK(cudaEventCreate(&t->ev0), "event");
     TCK(cudaEventCreate(&t->ev1), "event");
@@ -266,6 +268,7 @@ int gsb_tracker_set_map(gsb_tracker* t, int N, const float* means, const float* 
     TCK(cudaMemcpyAsync(t->quats, quats, sizeof(float) * 4 * (size_t)N, k, t->stream), "copy quats");
     TCK(cudaMemcpyAsync(t->scales, scales, sizeof(float) * 3 * (size_t)N, k, t->stream), "copy scales");
     TCK(cudaMemcpyAsync(t->opac, opacities, sizeof(float) * (size_t)N, k, t->stream), "copy opacities");
+    launch_map_iso(N, t->scales, t->iso_flag, t->stream);
     t->have_map = true; t->cap_dirty = true;
     return GSB_OK;
 }

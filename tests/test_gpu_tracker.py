@@ -308,3 +308,36 @@ def test_tracker_follows_the_reference_loop_fixture(gsb, tag, dl, nl):
     assert np.allclose(stf["q"], gold[tag + "_final_quat"], atol=5e-6)
     assert np.allclose(stf["t"], gold[tag + "_final_t"], atol=5e-6)
     trk.close()
+
+
+def test_one_iteration_anisotropic_map_matches_oracle(gsb):
+    """General Gaussians (random unit quaternions, three different scales): the tracker's lift takes its general path
+    (the isotropic short cut of raster_bwd.cu::lift_to_pose is off); loss within 1e-4, pose gradient within 1e-3."""
+    fp = U.frame(U.SMALL_CAM, stride=2, seed=21)
+    c2w0 = _start_pose(fp)
+    g = torch.Generator().manual_seed(5)
+    N = fp.tar_points.shape[0]
+    quats = torch.nn.functional.normalize(torch.randn(N, 4, generator=g, dtype=torch.float64), dim=-1)
+    scales = torch.tensor(fp.scales, dtype=torch.float64) * (0.6 + 0.8 * torch.rand(N, 3, generator=g, dtype=torch.float64))
+    means = torch.tensor(fp.tar_points, dtype=torch.float64)
+    opac = 0.3 + 0.7 * torch.rand(N, generator=g, dtype=torch.float64)
+    trk = gsb.PoseTracker(fp.W, fp.H, 1, gsb.TrackerConfig(early_stop=False))
+    trk.set_map(means.float().cuda(), quats.float().cuda(), scales.float().cuda(), opac.float().cuda())
+    trk.set_observation(torch.tensor(fp.src_depth).cuda(), fp.K)
+    trk.set_poses(c2w0, fp.src_c2w)
+    trk.run(1, poll_every=0, use_graph=False)
+    st = trk.states()[0]
+    dt = torch.float64
+    q = torch.tensor(orc.rotmat_to_quat(c2w0[:3, :3]), dtype=dt).requires_grad_(True)
+    t = torch.tensor(c2w0[:3, 3], dtype=dt).requires_grad_(True)
+    # the oracle sees the fp32-rounded map the kernel sees
+    tot, Ld, Ls, Ln, d, a, meta = orc.pose_loss(q, t, means.float().to(dt), quats.float().to(dt), scales.float().to(dt),
+                                                 opac.float().to(dt), torch.tensor(fp.src_depth, dtype=dt),
+                                                 torch.tensor(fp.K, dtype=dt), fp.W, fp.H)
+    tot.backward()
+    d_gpu, a_gpu = trk.render()
+    assert U.rel_err(d_gpu[0].cpu().numpy(), d.detach().numpy()) < 1e-4
+    assert abs(st["loss"] - float(tot)) / float(tot) < 1e-4
+    assert U.rel_err(st["g_q"], q.grad.numpy()) < 1e-3, (st["g_q"], q.grad)
+    assert U.rel_err(st["g_t"], t.grad.numpy()) < 1e-3, (st["g_t"], t.grad)
+    trk.close()
