@@ -261,7 +261,28 @@ __device__ __forceinline__ unsigned patch_mask(float mx, float my, float a, floa
     const unsigned xm = ((ux >= 0.5f && lx <= 7.5f) ? 1u : 0u) | ((ux >= 8.5f && lx <= 15.5f) ? 2u : 0u);
     const unsigned ys = ((uy >= 0.5f && ly <= 3.5f) ? 1u : 0u) | ((uy >= 4.5f && ly <= 7.5f) ? 4u : 0u) |
                         ((uy >= 8.5f && ly <= 11.5f) ? 16u : 0u) | ((uy >= 12.5f && ly <= 15.5f) ? 64u : 0u);
-    return xm * ys;                            // xm (2 bits) replicated at bit 2r for every reachable patch row r
+    unsigned m = xm * ys;                      // xm (2 bits) replicated at bit 2r for every reachable patch row r
+    // Second, corner-cutting test: sigma >= lambda_min/2 * |d|^2 (lambda_min = smallest eigenvalue of the conic), so a
+    // patch whose nearest pixel centre is farther than sqrt(2 tau / lambda_min) from the mean cannot be reached.
+    // Exact for circular footprints, still conservative for elongated ones (the box test above handles those).
+    const float hd = 0.5f * (a - c);
+    const float lmin = 0.5f * (a + c) - sqrtf(hd * hd + b * b) - 1e-6f * (a + c);   // minus a rounding-error bound
+    if (m != 0u && lmin > 0.f) {
+        const float r2 = __fdividef(2.f * tau, lmin) * 1.001f + 0.05f;
+        const float rx = mx - tile_x0, ry = my - tile_y0;
+        const float dx0 = fmaxf(0.f, fmaxf(0.5f - rx, rx - 7.5f)), dx1 = fmaxf(0.f, fmaxf(8.5f - rx, rx - 15.5f));
+        const float ex0 = dx0 * dx0, ex1 = dx1 * dx1;
+        unsigned keep = 0u;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const float dy = fmaxf(0.f, fmaxf((4.f * r + 0.5f) - ry, ry - (4.f * r + 3.5f)));
+            const float ey = dy * dy;
+            keep |= ((ex0 + ey <= r2) ? 1u : 0u) << (2 * r);
+            keep |= ((ex1 + ey <= r2) ? 2u : 0u) << (2 * r);
+        }
+        m &= keep;
+    }
+    return m;
 }
 
 }  // namespace gsb
