@@ -186,7 +186,7 @@ def run_native(args, rank, world, local_rank):
         return t.states()[0]                                                     # D2H
 
     # ---------------------------------------------------------------- device-resident leg (value)
-    for s in range(W_):
+    for s in range(max(W_, n_pool)):      # every tracker of the pool captures its CUDA graph before the timed region
         step_resident(s)
     launches0 = sum(t.counters()["total_launches"] for t in trackers)
     sampler = ClockSampler(local_rank) if rank == 0 else None
@@ -206,7 +206,7 @@ def run_native(args, rank, world, local_rank):
     M = int(np.mean([t.counters()["n_isects"] for t in trackers]))
 
     # ---------------------------------------------------------------- end-to-end leg (host buffers)
-    for s in range(min(W_, 2)):
+    for s in range(max(min(W_, 2), 1)):
         step_e2e(s)
     barrier()
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -23,15 +23,10 @@ __device__ __forceinline__ void kornia_rotmat(const float* q, float* R, float* q
     R[6] = txz - twy;         R[7] = tyz + twx;         R[8] = 1.f - (txx + tyy);
 }
 
-__global__ void pose_begin_kernel(int C, const gsb_pose_state* __restrict__ state, float* __restrict__ viewmats) {
-    int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
-    const gsb_pose_state& s = state[c];
-    if (s.stopped) return;
+// (quat_cur, t_cur) -> viewmat = inverse of [R t; 0 1] = [R^T  -R^T t; 0 1]
+__device__ __forceinline__ void write_viewmat(const gsb_pose_state& s, float* __restrict__ V) {
     float R[9], qn[4], n;
     kornia_rotmat(s.q, R, qn, &n);
-    float* V = viewmats + c * 16;
-    // inverse of [R t; 0 1] = [R^T  -R^T t; 0 1]
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
 #pragma unroll
@@ -39,6 +34,14 @@ __global__ void pose_begin_kernel(int C, const gsb_pose_state* __restrict__ stat
         V[i * 4 + 3] = -(R[0 * 3 + i] * s.t[0] + R[1 * 3 + i] * s.t[1] + R[2 * 3 + i] * s.t[2]);
     }
     V[12] = 0.f; V[13] = 0.f; V[14] = 0.f; V[15] = 1.f;
+}
+
+__global__ void pose_begin_kernel(int C, const gsb_pose_state* __restrict__ state, float* __restrict__ viewmats) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const gsb_pose_state& s = state[c];
+    if (s.stopped) return;
+    write_viewmat(s, viewmats + c * 16);
 }
 
 __device__ __forceinline__ void adam_update(float* p, float* m, float* v, const float* g, int n, float lr, float wd,
@@ -57,18 +60,19 @@ __device__ __forceinline__ void adam_update(float* p, float* m, float* v, const 
 
 __global__ void __launch_bounds__(256) pose_finish_kernel(
     int C, int n_tiles, int n_loss_blocks, const float* __restrict__ partials,
-    const float* __restrict__ loss_partials, const float* __restrict__ viewmats, gsb_pose_state* __restrict__ state,
+    const float* __restrict__ loss_partials, float* __restrict__ viewmats, gsb_pose_state* __restrict__ state,
     int* __restrict__ stop, gsb_tracker_config cfg, float inv_pixels, float inv_rows3,
     float* __restrict__ history, int history_cap) {
     __shared__ float red[15][8];
     const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    gsb_pose_state& s = state[c];
-    if (s.stopped) return;
+    if (state[c].stopped) return;
     // fixed-order two-level sums: 12 pose-gradient numbers over tiles, 2 loss sums over loss blocks
     float acc[15];
 #pragma unroll
     for (int k = 0; k < 15; ++k) acc[k] = 0.f;
+    // (independent loads, unrolled so that several L2 round trips are in flight per thread)
     const float* P = partials + (size_t)c * n_tiles * 12;
+#pragma unroll 4
     for (int i = tid; i < n_tiles; i += 256) {
         const float4* p4 = reinterpret_cast<const float4*>(P + (size_t)i * 12);
         float4 a = p4[0], b = p4[1], d = p4[2];
@@ -77,6 +81,7 @@ __global__ void __launch_bounds__(256) pose_finish_kernel(
         acc[8] += d.x; acc[9] += d.y; acc[10] += d.z; acc[11] += d.w;
     }
     const float* L = loss_partials + (size_t)c * n_loss_blocks * 3;
+#pragma unroll 4
     for (int i = tid; i < n_loss_blocks; i += 256) {
         acc[12] += L[i * 3];
         acc[13] += L[i * 3 + 1];
@@ -89,6 +94,7 @@ __global__ void __launch_bounds__(256) pose_finish_kernel(
     }
     __syncthreads();
     if (tid != 0) return;
+    gsb_pose_state s = state[c];   // one bulk read; every update below works on the copy, one bulk write at the end
     float g[15];
 #pragma unroll
     for (int k = 0; k < 15; ++k) {
@@ -98,7 +104,7 @@ __global__ void __launch_bounds__(256) pose_finish_kernel(
         g[k] = v;
     }
     // g[0..8] = d/dR_wc (row-major), g[9..11] = d/dt_wc
-    const float* V = viewmats + c * 16;
+    float* V = viewmats + c * 16;
     float R[9], qn[4], qnorm;
     kornia_rotmat(s.q, R, qn, &qnorm);
     float twc[3] = {V[3], V[7], V[11]};
@@ -171,6 +177,7 @@ __global__ void __launch_bounds__(256) pose_finish_kernel(
     }
     if (cfg.early_stop && s.counter >= cfg.patience) {
         s.stopped = 1;
+        state[c] = s;
         stop[c] = 1;
         return;  // the last gradient is discarded (break precedes optimizer_step)
     }
@@ -180,6 +187,8 @@ __global__ void __launch_bounds__(256) pose_finish_kernel(
     s.lr_q *= cfg.lr_gamma;
     s.lr_t *= cfg.lr_gamma;
     s.iter = iter + 1;
+    state[c] = s;
+    write_viewmat(s, V);   // the next iteration's world-to-camera matrix (pose_begin fused: one launch less)
 }
 
 void launch_pose_begin(int C, const gsb_pose_state* state, float* viewmats, cudaStream_t st) {
@@ -187,7 +196,7 @@ void launch_pose_begin(int C, const gsb_pose_state* state, float* viewmats, cuda
 }
 
 void launch_pose_finish(int C, int n_tiles, int n_loss_blocks, const float* partials, const float* loss_partials,
-                        const float* viewmats, gsb_pose_state* state, int* stop, gsb_tracker_config cfg,
+                        float* viewmats, gsb_pose_state* state, int* stop, gsb_tracker_config cfg,
                         float inv_pixels, float inv_rows3, float* history, int history_cap, cudaStream_t st) {
     pose_finish_kernel<<<C, 256, 0, st>>>(C, n_tiles, n_loss_blocks, partials, loss_partials, viewmats, state, stop,
                                           cfg, inv_pixels, inv_rows3, history, history_cap);

@@ -58,9 +58,9 @@ struct gsb_tracker {
     int64_t last_n_isects = 0;
 };
 
-static const int kStages = 9;   // profiled stages (the optional normal row-sum pass is timed inside "loss")
+static const int kStages = 9;   // slots of gsb_tracker_profile (slot 0, pose_begin, is fused away and reports 0)
 static int n_launches_per_iter(const gsb_tracker* t) {
-    return kStages + ((t->cfg.normal_lambda != 0.f && t->cfg.normal_mode == GSB_NORMAL_REFERENCE) ? 1 : 0);
+    return 8 + ((t->cfg.normal_lambda != 0.f && t->cfg.normal_mode == GSB_NORMAL_REFERENCE) ? 1 : 0);
 }
 
 static void invalidate_graph(gsb_tracker* t) {
@@ -77,8 +77,7 @@ static void enqueue_iteration(gsb_tracker* t, bool forward_only, cudaEvent_t* ma
     int mk = 0;
 #define GSB_MARK() do { if (marks) cudaEventRecord(marks[mk++], st); } while (0)
     GSB_MARK();
-    launch_pose_begin(C, t->state, t->viewmats, st);
-    GSB_MARK();
+    GSB_MARK();   // (pose_begin slot: the viewmats are written at set-up by ensure_capacity and afterwards by pose_finish)
     launch_project_bin(C, N, t->means, t->quats, t->scales, t->opac, t->viewmats, t->Ks, t->W, t->H, t->tile_w,
                        t->tile_h, c.eps2d, c.near_plane, c.far_plane, c.radius_clip, t->rec, t->bbox, t->counts,
                        t->stop, st);
@@ -403,7 +402,7 @@ int gsb_tracker_forward(gsb_tracker* t) {
     TCK(cudaMemcpyAsync(t->h_flags + t->C, t->n_isects, sizeof(int) * 2, cudaMemcpyDeviceToHost, t->stream), "flags");
     TCK(cudaStreamSynchronize(t->stream), "forward sync");
     TCK(cudaGetLastError(), "forward");
-    t->total_launches += 6;
+    t->total_launches += 5;
     t->last_n_isects = t->h_flags[t->C];
     return GSB_OK;
 }
