@@ -211,28 +211,64 @@ __global__ void __launch_bounds__(256) bin_emit_kernel(int CN, int N, const floa
                                                        int tile_h, int* __restrict__ cursor,
                                                        uint64_t* __restrict__ keys, int cap,
                                                        const int* __restrict__ stop) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= CN) return;
-    int c = i / N;
-    if (stop && stop[c]) return;
-    uint32_t x0, y0, x1, y1;
-    float depth;
-    if (PACKED) {
-        uint2 b = bbox[i];
-        x0 = b.x & 0xffffu; x1 = b.x >> 16; y0 = b.y & 0xffffu; y1 = b.y >> 16;
-        if (x1 <= x0 || y1 <= y0) return;
-        depth = rec[2 * (size_t)i].z;
-    } else {
-        int r = radii[i];
-        if (r <= 0) return;
-        tile_bbox(means2d[2 * i], means2d[2 * i + 1], r, tile_size, tile_w, tile_h, x0, y0, x1, y1);
-        depth = depths[i];
+    // Warp-aggregated emission: lanes whose Gaussians cover the SAME tile box (lattice neighbours mostly do) form a
+    // group; the group's leader reserves room for all of them with one atomicAdd per tile, so a tile's cursor sees
+    // one atomic per group instead of one per Gaussian.  Order inside a bin is irrelevant (tile_sort follows).
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    bool live = i < CN;
+    const int c = live ? i / N : 0;
+    if (live && stop && stop[c]) live = false;
+    uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0;
+    float depth = 0.f;
+    if (live) {
+        if (PACKED) {
+            uint2 b = bbox[i];
+            x0 = b.x & 0xffffu; x1 = b.x >> 16; y0 = b.y & 0xffffu; y1 = b.y >> 16;
+            if (x1 <= x0 || y1 <= y0) live = false;
+            else depth = rec[2 * (size_t)i].z;
+        } else {
+            int r = radii[i];
+            if (r <= 0) live = false;
+            else {
+                tile_bbox(means2d[2 * i], means2d[2 * i + 1], r, tile_size, tile_w, tile_h, x0, y0, x1, y1);
+                if (x1 <= x0 || y1 <= y0) live = false;
+                depth = depths[i];
+            }
+        }
     }
-    uint64_t key = ((uint64_t)(uint32_t)__float_as_int(depth) << 32) | (uint32_t)i;
+    // dead lanes carry a box no live lane can have (x1 <= x0) and leave right after the vote
+    const uint32_t kx = live ? (x0 | (x1 << 16)) : 0u;
+    const uint32_t ky = live ? (y0 | (y1 << 16)) : 0u;
+    const unsigned grp = __match_any_sync(0xffffffffu, kx) & __match_any_sync(0xffffffffu, ky) &
+                         __match_any_sync(0xffffffffu, live ? c : -1);
+    if (!live) return;
+    const int leader = __ffs(grp) - 1, cnt = __popc(grp), rank = __popc(grp & ((1u << lane) - 1u));
+    const uint64_t key = ((uint64_t)(uint32_t)__float_as_int(depth) << 32) | (uint32_t)i;
     int* cur = cursor + (size_t)c * tile_w * tile_h;
+    if (x1 - x0 <= 2 && y1 - y0 <= 2) {   // at most 2 x 2 tiles: the leader's atomics are issued back to back
+        const int t00 = y0 * tile_w + x0;
+        const bool hx = x1 - x0 > 1, hy = y1 - y0 > 1;
+        int b0 = 0, b1 = 0, b2 = 0, b3 = 0;
+        if (lane == leader) {
+            b0 = atomicAdd(cur + t00, cnt);
+            if (hx) b1 = atomicAdd(cur + t00 + 1, cnt);
+            if (hy) b2 = atomicAdd(cur + t00 + tile_w, cnt);
+            if (hx && hy) b3 = atomicAdd(cur + t00 + tile_w + 1, cnt);
+        }
+        b0 = __shfl_sync(grp, b0, leader) + rank; b1 = __shfl_sync(grp, b1, leader) + rank;
+        b2 = __shfl_sync(grp, b2, leader) + rank; b3 = __shfl_sync(grp, b3, leader) + rank;
+        if (b0 < cap) keys[b0] = key;
+        if (hx && b1 < cap) keys[b1] = key;
+        if (hy && b2 < cap) keys[b2] = key;
+        if (hx && hy && b3 < cap) keys[b3] = key;
+        return;
+    }
     for (uint32_t ty = y0; ty < y1; ++ty)
         for (uint32_t tx = x0; tx < x1; ++tx) {
-            int pos = atomicAdd(cur + ty * tile_w + tx, 1);
+            int base = 0;
+            if (lane == leader) base = atomicAdd(cur + ty * tile_w + tx, cnt);
+            const int pos = __shfl_sync(grp, base, leader) + rank;
             if (pos < cap) keys[pos] = key;
         }
 }
@@ -279,6 +315,86 @@ __device__ void bitonic_sort(uint64_t* a, int n, bool smem) {
     }
 }
 
+// Register-resident variant for bins of at most 256 * K keys (K = 2: the usual ~300-key bins of a depth lattice):
+// thread t owns elements K*t .. K*t+K-1 of the (virtually +inf padded) array.  Every round of the network pairs element
+// i with i ^ m (flip of a block h: m = h - 1; disperse at distance d: m = d), so a round is
+//   m < K        : compare-exchange inside the thread's registers,
+//   m < 32 * K   : one 64-bit shuffle per element with lane ^ (m / K),
+//   otherwise    : one trip through shared memory (double-buffered: one block barrier per round).
+// For 512 slots that is 9 register rounds, 30 shuffle rounds and 6 shared-memory rounds instead of 45 shared-memory
+// rounds.  Stages whose lower half already holds every real key (2^(lh-1) >= n) are skipped: the rest is +inf.
+template <int K>
+__device__ __forceinline__ void reg_sort_round(uint64_t (&v)[K], int m, bool flip, int tid, int lane, uint64_t* sbuf,
+                                               int& parity) {
+    constexpr int LGK = (K == 2) ? 1 : ((K == 4) ? 2 : 3);
+    if (m < K) {
+#pragma unroll
+        for (int mm = 1; mm < K; ++mm)
+            if (m == mm) {
+#pragma unroll
+                for (int e = 0; e < K; ++e)
+                    if ((e ^ mm) > e) {
+                        const uint64_t a = v[e], b = v[e ^ mm];
+                        v[e] = a < b ? a : b; v[e ^ mm] = a < b ? b : a;
+                    }
+            }
+        return;
+    }
+    const int off = m >> LGK;
+    if (off < 32) {
+        const int hb = flip ? ((off + 1) >> 1) : off;
+        const bool keep_min = !(lane & hb);
+        uint64_t nv[K];
+#pragma unroll
+        for (int e = 0; e < K; ++e) {
+            const uint64_t send = flip ? v[K - 1 - e] : v[e];
+            const uint64_t recv = __shfl_xor_sync(0xffffffffu, send, off);
+            const bool lt = v[e] < recv;
+            nv[e] = (lt == keep_min) ? v[e] : recv;
+        }
+#pragma unroll
+        for (int e = 0; e < K; ++e) v[e] = nv[e];
+        return;
+    }
+    uint64_t* buf = sbuf + parity * (256 * K);
+    parity ^= 1;
+#pragma unroll
+    for (int e = 0; e < K; ++e) buf[K * tid + e] = v[e];
+    __syncthreads();
+#pragma unroll
+    for (int e = 0; e < K; ++e) {
+        const int i = K * tid + e, j = i ^ m;
+        const uint64_t recv = buf[j];
+        const bool lt = v[e] < recv;
+        v[e] = (lt == (i < j)) ? v[e] : recv;
+    }
+}
+
+template <int K>
+__device__ __forceinline__ void reg_tile_sort(const uint64_t* __restrict__ g, int n, uint64_t* sbuf, int start,
+                                              int* __restrict__ flatten_ids, int64_t* __restrict__ isect_ids,
+                                              int64_t hi) {
+    constexpr int LGP = 8 + ((K == 2) ? 1 : ((K == 4) ? 2 : 3));
+    const int tid = threadIdx.x, lane = tid & 31;
+    uint64_t v[K];
+#pragma unroll
+    for (int e = 0; e < K; ++e) v[e] = (K * tid + e < n) ? g[K * tid + e] : ~0ull;
+    int parity = 0;
+    for (int lh = 1; lh <= LGP; ++lh) {
+        if ((1 << (lh - 1)) >= n) break;
+        reg_sort_round<K>(v, (1 << lh) - 1, true, tid, lane, sbuf, parity);
+        for (int ld = lh - 2; ld >= 0; --ld) reg_sort_round<K>(v, 1 << ld, false, tid, lane, sbuf, parity);
+    }
+#pragma unroll
+    for (int e = 0; e < K; ++e) {
+        const int i = K * tid + e;
+        if (i < n) {
+            flatten_ids[start + i] = (int)(uint32_t)v[e];
+            if (isect_ids) isect_ids[start + i] = hi | (int64_t)(v[e] >> 32);
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256) tile_sort_kernel(int n_tiles, int tile_bits, const int* __restrict__ offsets,
                                                         uint64_t* __restrict__ keys, int* __restrict__ flatten_ids,
                                                         int64_t* __restrict__ isect_ids, int cap,
@@ -291,6 +407,9 @@ __global__ void __launch_bounds__(256) tile_sort_kernel(int n_tiles, int tile_bi
     int n = end - start;
     if (n <= 0) return;
     uint64_t* g = keys + start;
+    const int64_t hi = ((int64_t)cam << (32 + tile_bits)) | ((int64_t)(bin % n_tiles) << 32);
+    if (n <= 512) { reg_tile_sort<2>(g, n, sk, start, flatten_ids, isect_ids, hi); return; }
+    if (n <= 1024) { reg_tile_sort<4>(g, n, sk, start, flatten_ids, isect_ids, hi); return; }
     uint64_t* a = g;
     if (n <= SORT_SMEM) {
         for (int i = threadIdx.x; i < n; i += blockDim.x) sk[i] = g[i];
@@ -298,7 +417,6 @@ __global__ void __launch_bounds__(256) tile_sort_kernel(int n_tiles, int tile_bi
     }
     __syncthreads();
     if (n > 1) bitonic_sort(a, n, n <= SORT_SMEM);
-    int64_t hi = ((int64_t)cam << (32 + tile_bits)) | ((int64_t)(bin % n_tiles) << 32);
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
         uint64_t k = a[i];
         flatten_ids[start + i] = (int)(uint32_t)k;

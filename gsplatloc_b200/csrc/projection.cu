@@ -137,27 +137,38 @@ __global__ void __launch_bounds__(256) project_bin_kernel(
     const float* __restrict__ opacities, const float* __restrict__ viewmats, const float* __restrict__ Ks, int W, int H,
     int tile_w, int tile_h, float eps2d, float near_plane, float far_plane, float radius_clip,
     float4* __restrict__ rec, uint2* __restrict__ bbox, int* __restrict__ counts, const int* __restrict__ stop) {
-    int n = blockIdx.x * blockDim.x + threadIdx.x;
-    int c = blockIdx.y;
-    if (n >= N) return;
-    if (stop && stop[c]) return;
-    Cam cam = load_cam(viewmats + c * 16, Ks + c * 9);
-    GaussIn g = load_gauss(means, quats, scales, n);
-    Proj p; float S[6], Sc[6];
-    bool ok = project_gaussian(cam, g.mean, g.q, g.s, W, H, eps2d, near_plane, far_plane, radius_clip, p, S, Sc);
-    size_t i = (size_t)c * N + n;
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    const int c = blockIdx.y;
+    if (stop && stop[c]) return;   // uniform over the block
+    const bool live = n < N;
+    const int lane = threadIdx.x & 31;
     uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0;
-    if (ok) {
-        tile_bbox(p.mx, p.my, p.radius, GSB_TILE, tile_w, tile_h, x0, y0, x1, y1);
-        rec[2 * i] = make_float4(p.mx, p.my, p.pz, opacities[n]);
-        rec[2 * i + 1] = make_float4(p.ca, p.cb, p.cc, __int_as_float(p.radius));
-        int* cnt = counts + (size_t)c * tile_w * tile_h;
-        for (uint32_t ty = y0; ty < y1; ++ty)
-            for (uint32_t tx = x0; tx < x1; ++tx) atomicAdd(cnt + ty * tile_w + tx, 1);
-    } else {
-        rec[2 * i + 1] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
+    bool ok = false;
+    if (live) {
+        Cam cam = load_cam(viewmats + c * 16, Ks + c * 9);
+        GaussIn g = load_gauss(means, quats, scales, n);
+        Proj p; float S[6], Sc[6];
+        ok = project_gaussian(cam, g.mean, g.q, g.s, W, H, eps2d, near_plane, far_plane, radius_clip, p, S, Sc);
+        const size_t i = (size_t)c * N + n;
+        if (ok) {
+            tile_bbox(p.mx, p.my, p.radius, GSB_TILE, tile_w, tile_h, x0, y0, x1, y1);
+            rec[2 * i] = make_float4(p.mx, p.my, p.pz, opacities[n]);
+            rec[2 * i + 1] = make_float4(p.ca, p.cb, p.cc, __int_as_float(p.radius));
+        } else {
+            rec[2 * i + 1] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
+        }
+        bbox[i] = make_uint2(x0 | (x1 << 16), y0 | (y1 << 16));
     }
-    bbox[i] = make_uint2(x0 | (x1 << 16), y0 | (y1 << 16));
+    // Histogram, warp-aggregated: lanes with the same tile box vote, the group's leader adds the group size once per
+    // tile (RED, no return) -- a tile counter sees one atomic per group of lattice neighbours, not one per Gaussian.
+    const bool any_tile = ok && x1 > x0 && y1 > y0;
+    const unsigned grp = __match_any_sync(0xffffffffu, any_tile ? (x0 | (x1 << 16)) : 0u) &
+                         __match_any_sync(0xffffffffu, any_tile ? (y0 | (y1 << 16)) : 0u);
+    if (!any_tile || lane != __ffs(grp) - 1) return;
+    const int cnt = __popc(grp);
+    int* hist = counts + (size_t)c * tile_w * tile_h;
+    for (uint32_t ty = y0; ty < y1; ++ty)
+        for (uint32_t tx = x0; tx < x1; ++tx) atomicAdd(hist + ty * tile_w + tx, cnt);
 }
 
 void launch_project_fwd(int C, int N, const float* means, const float* quats, const float* scales,

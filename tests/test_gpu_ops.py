@@ -138,10 +138,12 @@ def test_isect_ties_and_empty(ops, method):
     assert off.shape == (2, 2, 3) and int(off.abs().sum()) == 0
 
 
-def test_isect_big_bins_sort_in_global_memory(ops):
-    # > 4096 Gaussians in one tile exercises the out-of-shared-memory branch of the tile sort
-    rng = np.random.default_rng(6)
-    N = 6000
+@pytest.mark.parametrize("N", [1, 2, 3, 31, 33, 64, 65, 255, 256, 257, 300, 511, 512, 513, 700, 1023, 1024, 1025, 2500,
+                               4096, 4097, 6000])
+def test_isect_bin_sizes_cover_every_sort_branch(ops, N):
+    # all N Gaussians land in tile (0,0) (and spill into its neighbours): bins of <= 512 keys take the register
+    # network with 2 keys per thread, <= 1024 with 4, <= 4096 the shared-memory network, larger ones sort in HBM
+    rng = np.random.default_rng(6 + N)
     m2 = (rng.uniform(2, 14, (1, N, 2))).astype(np.float32)
     radii = np.full((1, N), 1, dtype=np.int32)
     dep = rng.uniform(0.5, 5.0, (1, N)).astype(np.float32)
