@@ -237,18 +237,21 @@ __global__ void __launch_bounds__(256) bin_emit_kernel(int CN, int N, const floa
             }
         }
     }
-    // dead lanes carry a box no live lane can have (x1 <= x0) and leave right after the vote
-    const uint32_t kx = live ? (x0 | (x1 << 16)) : 0u;
-    const uint32_t ky = live ? (y0 | (y1 << 16)) : 0u;
-    const unsigned grp = __match_any_sync(0xffffffffu, kx) & __match_any_sync(0xffffffffu, ky) &
-                         __match_any_sync(0xffffffffu, live ? c : -1);
-    if (!live) return;
-    const int leader = __ffs(grp) - 1, cnt = __popc(grp), rank = __popc(grp & ((1u << lane) - 1u));
+    const uint32_t bw = x1 - x0, bh = y1 - y0;
+    const bool small = live && bw <= 2 && bh <= 2;
     const uint64_t key = ((uint64_t)(uint32_t)__float_as_int(depth) << 32) | (uint32_t)i;
-    int* cur = cursor + (size_t)c * tile_w * tile_h;
-    if (x1 - x0 <= 2 && y1 - y0 <= 2) {   // at most 2 x 2 tiles: the leader's atomics are issued back to back
+    const int n_tiles_cam = tile_w * tile_h;
+    // ---- boxes of at most 2 x 2 tiles (two thirds of a depth lattice): grouped, the leader's atomics back to back.
+    // Other lanes carry a box no small lane can have and form no group that matters.
+    const uint32_t kx = small ? (x0 | (x1 << 16)) : 0u;
+    const uint32_t ky = small ? (y0 | (y1 << 16)) : 0u;
+    const unsigned grp = __match_any_sync(0xffffffffu, kx) & __match_any_sync(0xffffffffu, ky) &
+                         __match_any_sync(0xffffffffu, small ? c : -1);
+    if (small) {
+        const int leader = __ffs(grp) - 1, cnt = __popc(grp), rank = __popc(grp & ((1u << lane) - 1u));
+        int* cur = cursor + (size_t)c * n_tiles_cam;
         const int t00 = y0 * tile_w + x0;
-        const bool hx = x1 - x0 > 1, hy = y1 - y0 > 1;
+        const bool hx = bw > 1, hy = bh > 1;
         int b0 = 0, b1 = 0, b2 = 0, b3 = 0;
         if (lane == leader) {
             b0 = atomicAdd(cur + t00, cnt);
@@ -262,15 +265,42 @@ __global__ void __launch_bounds__(256) bin_emit_kernel(int CN, int N, const floa
         if (hx && b1 < cap) keys[b1] = key;
         if (hy && b2 < cap) keys[b2] = key;
         if (hx && hy && b3 < cap) keys[b3] = key;
-        return;
     }
-    for (uint32_t ty = y0; ty < y1; ++ty)
-        for (uint32_t tx = x0; tx < x1; ++tx) {
-            int base = 0;
-            if (lane == leader) base = atomicAdd(cur + ty * tile_w + tx, cnt);
-            const int pos = __shfl_sync(grp, base, leader) + rank;
-            if (pos < cap) keys[pos] = key;
+    // ---- larger boxes: their (Gaussian, tile) pairs are flattened over the warp, 32 pairs per round, so that the
+    // longest dependent chain of atomics is ceil(pairs / 32) round trips and not the tile count of the widest box.
+    const int mine = (live && !small) ? (int)(bw * bh) : 0;
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int up = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += up;
+    }
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    if (total == 0) return;
+    __shared__ int s_incl[8][32];
+    int* wincl = s_incl[threadIdx.x >> 5];
+    wincl[lane] = incl;
+    __syncwarp();
+    const int excl = incl - mine;
+    const uint32_t key_hi = (uint32_t)__float_as_int(depth);
+    for (int w0 = 0; w0 < total; w0 += 32) {
+        const int w = w0 + lane;
+        int src = 0;   // the first lane whose inclusive sum exceeds w
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1)
+            if (wincl[src + step - 1] <= w) src += step;
+        src = min(src, 31);
+        const uint32_t sx0 = __shfl_sync(0xffffffffu, x0, src), sy0 = __shfl_sync(0xffffffffu, y0, src);
+        const uint32_t sbw = __shfl_sync(0xffffffffu, bw, src);
+        const int sexcl = __shfl_sync(0xffffffffu, excl, src), sc = __shfl_sync(0xffffffffu, c, src);
+        const uint32_t shi = __shfl_sync(0xffffffffu, key_hi, src), slo = __shfl_sync(0xffffffffu, (uint32_t)i, src);
+        if (w < total) {
+            const uint32_t t = (uint32_t)(w - sexcl);
+            const uint32_t ty = sy0 + t / sbw, tx = sx0 + t % sbw;
+            const int pos = atomicAdd(cursor + (size_t)sc * n_tiles_cam + ty * tile_w + tx, 1);
+            if (pos < cap) keys[pos] = ((uint64_t)shi << 32) | slo;
         }
+    }
 }
 
 // One block per (camera, tile): sort the bin ascending by the unique 64-bit (depth bits, flat index) key.
