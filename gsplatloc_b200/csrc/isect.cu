@@ -410,10 +410,14 @@ __device__ __forceinline__ void reg_tile_sort(const uint64_t* __restrict__ g, in
 #pragma unroll
     for (int e = 0; e < K; ++e) v[e] = (K * tid + e < n) ? g[K * tid + e] : ~0ull;
     int parity = 0;
+    // fully unrolled: m, the lane offset and the min/max side of every round are immediates
+#pragma unroll
     for (int lh = 1; lh <= LGP; ++lh) {
-        if ((1 << (lh - 1)) >= n) break;
-        reg_sort_round<K>(v, (1 << lh) - 1, true, tid, lane, sbuf, parity);
-        for (int ld = lh - 2; ld >= 0; --ld) reg_sort_round<K>(v, 1 << ld, false, tid, lane, sbuf, parity);
+        if ((1 << (lh - 1)) < n) {
+            reg_sort_round<K>(v, (1 << lh) - 1, true, tid, lane, sbuf, parity);
+#pragma unroll
+            for (int ld = lh - 2; ld >= 0; --ld) reg_sort_round<K>(v, 1 << ld, false, tid, lane, sbuf, parity);
+        }
     }
 #pragma unroll
     for (int e = 0; e < K; ++e) {

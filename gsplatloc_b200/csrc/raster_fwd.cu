@@ -27,8 +27,11 @@ __device__ __forceinline__ unsigned stage_gaussian(float* __restrict__ dst, int 
                                                    float tile_x0, float tile_y0) {
     if (PACKED) {
         const float4 r0 = __ldg(rec + 2 * (size_t)g), r1 = __ldg(rec + 2 * (size_t)g + 1);
-        reinterpret_cast<float4*>(dst)[0] = make_float4(r0.x, r0.y, r1.x, r1.y);
-        reinterpret_cast<float4*>(dst)[1] = make_float4(r1.z, r0.w, r0.z, 0.f);
+        // conic pre-scaled so that the inner loop gets the ex2 argument directly:
+        //   -log2(e) * sigma = a' dx^2 + b' dx dy + c' dy^2,  a' = -log2(e)/2 a, b' = -log2(e) b, c' = -log2(e)/2 c
+        // (the raster backward replays with the same pre-scaled form)
+        reinterpret_cast<float4*>(dst)[0] = make_float4(r0.x, r0.y, -0.72134752044448170f * r1.x, -1.4426950408889634f * r1.y);
+        reinterpret_cast<float4*>(dst)[1] = make_float4(-0.72134752044448170f * r1.z, r0.w, r0.z, 0.f);
         return patch_mask(r0.x, r0.y, r1.x, r1.y, r1.z, r0.w, tile_x0, tile_y0);
     } else {
         const float2 xy = reinterpret_cast<const float2*>(means2d)[g];
@@ -98,10 +101,21 @@ __global__ void __launch_bounds__(256) raster_fwd_kernel(
                 const float4 p0 = reinterpret_cast<const float4*>(sm + t * RS)[0];
                 const float4 p1 = reinterpret_cast<const float4*>(sm + t * RS)[1];
                 const float dx = p0.x - px, dy = p0.y - py;
-                const float sigma = 0.5f * (p0.z * dx * dx + p1.x * dy * dy) + p0.w * dx * dy;
-                const float alpha = fminf(GSB_ALPHA_MAX, p1.y * exp_neg_fast(sigma));
+                float alpha;
+                bool behind;   // sigma < 0: not a valid Gaussian falloff (A.4)
+                if (PACKED) {
+                    const float e = fmaf(dx, fmaf(p0.z, dx, p0.w * dy), p1.x * dy * dy);
+                    float vis;
+                    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(vis) : "f"(e));
+                    alpha = fminf(GSB_ALPHA_MAX, p1.y * vis);
+                    behind = e > 0.f;
+                } else {
+                    const float sigma = 0.5f * (p0.z * dx * dx + p1.x * dy * dy) + p0.w * dx * dy;
+                    alpha = fminf(GSB_ALPHA_MAX, p1.y * exp_neg_fast(sigma));
+                    behind = sigma < 0.f;
+                }
                 const float next_T = T * (1.f - alpha);
-                const bool hit = !done && !(sigma < 0.f || alpha < GSB_ALPHA_MIN);
+                const bool hit = !done && !(behind || alpha < GSB_ALPHA_MIN);
                 const bool comp = hit && next_T > GSB_T_STOP;   // an entry that would end the pixel is NOT composited
                 done = done || (hit && !comp);
                 if (comp) {
