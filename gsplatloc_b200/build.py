@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libgsplatloc_b200.so")
-SOURCES = ["projection", "isect", "raster_fwd", "raster_bwd", "loss", "pose", "sh", "capi", "tracker"]
+SOURCES = ["projection", "isect", "raster_fwd", "raster_bwd", "loss", "pose", "sh", "knn", "geometry", "capi", "tracker"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
               "-Wno-deprecated-declarations"]
 

@@ -241,4 +241,41 @@ int gsb_depth_edge_normal_loss(int C, int width, int height, const float* depth,
     return GSB_OK;
 }
 
+// ---- per-frame setup (rows f1, f2)
+int gsb_knn_sq_dists(int N, const float* points, int k, float* sq_dists, int* grid_dims_host, void* stream) {
+    if (N < 0 || k < 1 || k > 32) return fail(GSB_ERR_ARG, "gsb_knn_sq_dists: need N >= 0 and 1 <= k <= 32", cudaSuccess);
+    if (N > 0 && (!points || !sq_dists)) return fail(GSB_ERR_ARG, "gsb_knn_sq_dists: null pointer", cudaSuccess);
+    const char* what = "";
+    cudaError_t e = knn_run(N, points, k, sq_dists, nullptr, 0.f, 1, grid_dims_host, (cudaStream_t)stream, &what);
+    if (e != cudaSuccess) return fail(e == cudaErrorInvalidValue ? GSB_ERR_ARG : GSB_ERR_CUDA, what, e);
+    return GSB_OK;
+}
+
+int gsb_init_gs_scales(int N, const float* points, int k, float eps, int dist_is_squared, float* scales, void* stream) {
+    if (N < 0 || k < 2 || k > 32) return fail(GSB_ERR_ARG, "gsb_init_gs_scales: need N >= 0 and 2 <= k <= 32", cudaSuccess);
+    if (N > 0 && (!points || !scales)) return fail(GSB_ERR_ARG, "gsb_init_gs_scales: null pointer", cudaSuccess);
+    const char* what = "";
+    cudaError_t e = knn_run(N, points, k, nullptr, scales, eps, dist_is_squared, nullptr, (cudaStream_t)stream, &what);
+    if (e != cudaSuccess) return fail(e == cudaErrorInvalidValue ? GSB_ERR_ARG : GSB_ERR_CUDA, what, e);
+    return GSB_OK;
+}
+
+int gsb_depth_to_points(int width, int height, const float* depth, const float* K_host, const float* T_host,
+                        float* points, void* stream) {
+    if (width < 0 || height < 0) return fail(GSB_ERR_ARG, "gsb_depth_to_points: bad sizes", cudaSuccess);
+    if (!K_host || ((size_t)width * height > 0 && (!depth || !points)))
+        return fail(GSB_ERR_ARG, "gsb_depth_to_points: null pointer", cudaSuccess);
+    launch_depth_to_points(width, height, depth, K_host, T_host, points, (cudaStream_t)stream);
+    CK_LAUNCH("gsb_depth_to_points");
+    return GSB_OK;
+}
+
+int gsb_transform_points(int N, const float* points_in, const float* T_host, float* points_out, void* stream) {
+    if (N < 0 || !T_host || (N > 0 && (!points_in || !points_out)))
+        return fail(GSB_ERR_ARG, "gsb_transform_points: bad arguments", cudaSuccess);
+    launch_transform_points(N, points_in, T_host, points_out, (cudaStream_t)stream);
+    CK_LAUNCH("gsb_transform_points");
+    return GSB_OK;
+}
+
 }  // extern "C"

@@ -88,4 +88,12 @@ void launch_sh_fwd(int n, int K, int degree, const float* dirs, const float* coe
 void launch_sh_bwd(int n, int K, int degree, const float* dirs, const float* coeffs, const uint8_t* masks,
                    const float* v_colors, float* v_coeffs, float* v_dirs, cudaStream_t st);
 
+
+// ---- knn.cu / geometry.cu (per-frame setup around the loop)
+cudaError_t knn_run(int N, const float* pts, int k, float* sq_dists, float* scales, float eps, int dist_is_squared,
+                    int* grid_dims_out, cudaStream_t st, const char** what);
+void launch_depth_to_points(int W, int H, const float* depth, const float* K9_host, const float* T16_host,
+                            float* points, cudaStream_t st);
+void launch_transform_points(int N, const float* in, const float* T16_host, float* out, cudaStream_t st);
+
 }  // namespace gsb

@@ -188,6 +188,26 @@ int gsb_tracker_profile(gsb_tracker* t, int n_iters, float* stage_ms_host);
 /* one forward only (render at the current poses; used for the GT re-render of geometry.py:69-135) */
 int gsb_tracker_forward(gsb_tracker* t);
 
+/* ---------------------------------------------------------------------------------------------------------------
+ * Per-frame setup around the loop.  DEVICE pointers unless named *_host.
+ * ------------------------------------------------------------------------------------------------------------- */
+/* knn (src/my_gsplat/utils.py:16-22: small_gicp.KdTree(...).batch_knn_search(x, k) second return value): for every
+ * point the k smallest SQUARED distances to the points of the same cloud, ascending; column 0 is the point itself (0).
+ * points [N,3] -> sq_dists [N,k].  1 <= k <= 32.  Exact (uniform grid, expanding shells).  Synchronises the stream
+ * twice (grid sizing) and allocates its scratch with cudaMallocAsync on it.  grid_dims_host[3] (nullable): cells. */
+int gsb_knn_sq_dists(int N, const float* points, int k, float* sq_dists, int* grid_dims_host, void* stream);
+/* init_gs_scales (src/my_gsplat/geometry.py:44-66): scales[N,3] = sqrt(mean(dist[:,1:]**2) + eps) repeated 3 times,
+ * dist = knn(points, k).  dist_is_squared = 0: the literal reference (knn() hands back small_gicp's squared distances
+ * and they are squared again); 1: dist are true distances, i.e. the RMS neighbour distance. */
+int gsb_init_gs_scales(int N, const float* points, int k, float eps, int dist_is_squared, float* scales, void* stream);
+/* depth_to_points (geometry.py:138-161, kornia depth_to_3d_v2): depth [H,W] -> points [H*W,3] =
+ * depth * ((x-cx)/fx, (y-cy)/fy, 1); T_host (nullable, row-major 4x4) applies transform_points (geometry.py:23-41)
+ * in the same pass.  K_host: row-major 3x3. */
+int gsb_depth_to_points(int width, int height, const float* depth, const float* K_host, const float* T_host,
+                        float* points, void* stream);
+/* transform_points (geometry.py:23-41): out[N,3] = in @ R^T + t, T_host row-major 4x4. in == out allowed. */
+int gsb_transform_points(int N, const float* points_in, const float* T_host, float* points_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

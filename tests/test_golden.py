@@ -91,3 +91,46 @@ def test_pose_module_and_metrics_match_reference(gold):
         assert np.allclose(c.numpy(), c2w, atol=2e-6)
         e = orc.pose_errors(c2w, other)
         assert abs(e[0] - eT) < 1e-6 and abs(e[1] - eR) < 5e-3
+
+
+# ------------------------------------------------------------------------------- per-frame setup (rows f1, f2)
+GOLDEN_GEO = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_geometry_small.npz")
+
+
+@pytest.fixture(scope="module")
+def gold_geo():
+    return dict(np.load(GOLDEN_GEO))
+
+
+@pytest.mark.parametrize("tag", ["lattice", "blob"])
+@pytest.mark.parametrize("k", [5, 4])
+def test_geometry_oracle_knn_and_scales_match_reference_code(gold_geo, tag, k):
+    """oracle/geometry_oracle.py against the reference's own knn + init_gs_scales (make_golden_geometry.py).
+    Tolerance: 1e-6 relative (float32 fixture)."""
+    from oracle import geometry_oracle as geo
+    pts = gold_geo[tag + "_points"]
+    d = geo.knn_sq_dists(pts, k).astype(np.float32)
+    assert np.allclose(d, gold_geo[f"{tag}_knn{k}"], rtol=1e-6, atol=1e-12)
+    s = geo.init_gs_scales(pts, k)
+    assert s.shape == (pts.shape[0], 3)
+    assert np.allclose(s, gold_geo[f"{tag}_scales{k}"], rtol=2e-6, atol=0)
+    # the non-literal variant is the RMS distance to the k-1 neighbours
+    rms = geo.init_gs_scales(pts, k, reference_faithful=False)[:, 0]
+    assert np.allclose(rms, np.sqrt(gold_geo[f"{tag}_knn{k}"][:, 1:].mean(-1) + 1e-24), rtol=2e-6)
+
+
+def test_geometry_oracle_points_match_reference_code(gold_geo):
+    from oracle import geometry_oracle as geo
+    assert np.allclose(geo.transform_points(gold_geo["T"], gold_geo["lattice_points"]), gold_geo["lattice_transformed"],
+                       rtol=1e-6, atol=1e-6)
+    p = geo.depth_to_points(gold_geo["depth"], gold_geo["K"])
+    assert p.shape == gold_geo["depth_points"].shape
+    assert np.array_equal(p, gold_geo["depth_points"])        # same float32 operations in the same order
+
+
+def test_geometry_oracle_depth_gt_matches_reference_code(gold_geo):
+    from oracle import geometry_oracle as geo
+    W, H = int(gold_geo["cam"][0]), int(gold_geo["cam"][1])
+    d = geo.compute_depth_gt(gold_geo["gt_points"], gold_geo["K"], gold_geo["gt_c2w"], H, W)
+    assert d.shape == (H, W)
+    assert U.rel_err(d, gold_geo["gt_depth"]) < 1e-5
