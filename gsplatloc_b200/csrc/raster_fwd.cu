@@ -55,8 +55,11 @@ __global__ void __launch_bounds__(256) raster_fwd_kernel(
     float* __restrict__ render_alphas, int* __restrict__ last_ids, int normalize_last, const int* __restrict__ stop,
     unsigned char* __restrict__ masks_out) {
     constexpr int RS = RecStride<CDIM>::value;
-    __shared__ __align__(16) float sm[256 * RS];
-    __shared__ unsigned char s_mask[256];
+    // FB records per staging round: 512 on the tracker path (a depth lattice puts ~300 Gaussians in a tile, so most
+    // tiles need ONE round: one barrier pair and one dependent ids -> records load chain instead of two)
+    constexpr int FB = PACKED ? 512 : 256;
+    __shared__ __align__(16) float sm[FB * RS];
+    __shared__ unsigned char s_mask[FB];
     const int cam = blockIdx.z;
     if (stop && stop[cam]) return;
     const int tile_id = blockIdx.y * tile_w + blockIdx.x;
@@ -71,7 +74,7 @@ __global__ void __launch_bounds__(256) raster_fwd_kernel(
     const int bin = cam * tile_w * tile_h + tile_id;
     const int range_start = tile_offsets[bin];
     const int range_end = (bin == C * tile_w * tile_h - 1) ? n_isects : tile_offsets[bin + 1];
-    const int num_batches = (range_end - range_start + 255) / 256;
+    const int num_batches = (range_end - range_start + FB - 1) / FB;
 
     float T = 1.f;
     int cur_idx = 0;
@@ -82,17 +85,21 @@ __global__ void __launch_bounds__(256) raster_fwd_kernel(
 
     for (int b = 0; b < num_batches; ++b) {
         if (__syncthreads_count(done) >= 256) break;
-        const int batch_start = range_start + 256 * b;
-        const int idx = batch_start + tid;
-        unsigned m = 0u;
-        if (idx < range_end)
-            m = stage_gaussian<CDIM, PACKED>(sm + tid * RS, flatten_ids[idx], rec, means2d, conics, colors, opacities,
-                                             tile_x0, tile_y0);
-        s_mask[tid] = (unsigned char)m;
-        if (masks_out && idx < range_end) masks_out[idx] = (unsigned char)m;   // reused by the backward's gather
+        const int batch_start = range_start + FB * b;
+#pragma unroll
+        for (int u = 0; u < FB / 256; ++u) {
+            const int slot = tid + 256 * u;
+            const int idx = batch_start + slot;
+            unsigned m = 0u;
+            if (idx < range_end)
+                m = stage_gaussian<CDIM, PACKED>(sm + slot * RS, flatten_ids[idx], rec, means2d, conics, colors,
+                                                 opacities, tile_x0, tile_y0);
+            s_mask[slot] = (unsigned char)m;
+            if (masks_out && idx < range_end) masks_out[idx] = (unsigned char)m;   // reused by the backward's gather
+        }
         __syncthreads();
         if (warp_done) continue;
-        const int batch_size = min(256, range_end - batch_start);
+        const int batch_size = min(FB, range_end - batch_start);
         for (int c0 = 0; c0 < batch_size; c0 += 32) {
             unsigned bits = __ballot_sync(0xffffffffu, ((unsigned)s_mask[c0 + lane] >> wid) & 1u);
             while (bits) {
