@@ -37,6 +37,7 @@ WORKLOADS = {
     "replica50k": ("REPLICA", 4, 2.0, 1.0),       # configs[0]               (S1)
     "tum77k": ("TUM", 2, 6.0, 3.0),               # configs[2]               (S3)
     "hd500k": ("HD", 2, 2.0, 1.0),                # towards configs[4]       (S5)
+    "hd2m": ("HD", 1, 2.0, 1.0),                  # configs[4]: 1920x1080, 2.07 M Gaussians (S5)
 }
 
 
@@ -145,7 +146,25 @@ def run_native(args, rank, world, local_rank):
     K, W_, iters = args.steps, args.warmup, args.iters
     n_pool = args.pool
     frames = make_frames(args.workload, n_pool, seed0=42 + 1000 * rank)     # rank r owns its own frames
-    cfg = TrackerConfig(max_steps=args.max_steps, early_stop=False)          # fixed 100 steps for timing (S2)
+    Cn = max(1, args.cameras)                                                # pose hypotheses per frame (configs[3])
+    cfg = TrackerConfig(max_steps=args.max_steps, early_stop=False,          # fixed 100 steps for timing (S2)
+                        depth_lambda=args.depth_lambda, normal_lambda=args.normal_lambda)
+
+    def start_poses(fp, seed):
+        """configs[3] (S4): the start pose perturbed by N(0, (1 cm)^2), N(0, (0.5 deg)^2) per hypothesis."""
+        if Cn == 1:
+            return fp.tar_c2w
+        from gsplatloc_b200 import synthetic as syn
+        rng = np.random.default_rng(seed)
+        out = []
+        for c in range(Cn):
+            p = fp.tar_c2w.copy()
+            if c:
+                p[:3, 3] += rng.normal(0, 0.01, 3).astype(np.float32)
+                r = np.deg2rad(rng.normal(0, 0.5, 3))
+                p[:3, :3] = (p[:3, :3] @ syn._rot_xyz(*r)).astype(np.float32)
+            out.append(p)
+        return np.stack(out)
     host = []
     trackers = []
     stream = torch.cuda.Stream(dev)          # every tracker launches here; the timing events are recorded here
@@ -157,10 +176,11 @@ def run_native(args, rank, world, local_rank):
                    scales=torch.tensor(fp.scales).pin_memory(), opac=torch.ones(N).pin_memory(),
                    depth=obs.cpu().pin_memory())
         host.append(pin)
-        t = PoseTracker(fp.W, fp.H, 1, cfg, device=dev, stream=stream)
+        t = PoseTracker(fp.W, fp.H, Cn, cfg, device=dev, stream=stream)
         t.set_map(pin["means"].to(dev), pin["quats"].to(dev), pin["scales"].to(dev), pin["opac"].to(dev))
         t.set_observation(obs, fp.K)
-        t.set_poses(fp.tar_c2w, fp.src_c2w)
+        pin["start"] = start_poses(fp, 7 + len(trackers))
+        t.set_poses(pin["start"], fp.src_c2w)
         trackers.append(t)
     fp0 = frames[0]
     N, P = fp0.tar_points.shape[0], fp0.W * fp0.H
@@ -173,7 +193,7 @@ def run_native(args, rank, world, local_rank):
 
     def step_resident(s):
         t, fp = trackers[s % n_pool], frames[s % n_pool]
-        t.set_poses(fp.tar_c2w, fp.src_c2w)
+        t.set_poses(host[s % n_pool]["start"], fp.src_c2w)
         t.run(iters, poll_every=0, use_graph=True)
         return t
 
@@ -181,7 +201,7 @@ def run_native(args, rank, world, local_rank):
         t, fp, pin = trackers[s % n_pool], frames[s % n_pool], host[s % n_pool]
         t.set_map(pin["means"], pin["quats"], pin["scales"], pin["opac"])        # H2D from pinned memory
         t.set_observation(pin["depth"], fp.K)                                    # H2D
-        t.set_poses(fp.tar_c2w, fp.src_c2w)
+        t.set_poses(pin["start"], fp.src_c2w)
         t.run(iters, poll_every=0, use_graph=True)
         return t.states()[0]                                                     # D2H
 
@@ -216,14 +236,14 @@ def run_native(args, rank, world, local_rank):
     e3.record(stream)
     barrier()
     ms_e2e = e2.elapsed_time(e3)
-    h2d = int(sum(v.numel() * 4 for v in host[0].values())) + 16 * 4 * 2 + 9 * 4
-    d2h = int(__import__("ctypes").sizeof(_lib.PoseState))
+    h2d = int(sum(v.numel() * 4 for v in host[0].values() if torch.is_tensor(v))) + 16 * 4 * (Cn + 1) + 9 * 4
+    d2h = int(__import__("ctypes").sizeof(_lib.PoseState)) * Cn
 
     # ---------------------------------------------------------------- per-kernel times (roofline), rank 0 only
     stage_ms = None
     if rank == 0:
         t = trackers[0]
-        t.set_poses(frames[0].tar_c2w, frames[0].src_c2w)
+        t.set_poses(host[0]["start"], frames[0].src_c2w)
         t.profile(3)
         stage_ms = t.profile(20)
 
@@ -238,25 +258,26 @@ def run_native(args, rank, world, local_rank):
     records = sharding.gather_records(records, dev)        # the path's one collective: final gather of pose errors
     if rank != 0:
         return
-    total_iters = K * iters * world
+    total_iters = K * iters * world * Cn     # every hypothesis of every frame advances one iteration per launch set
     value = total_iters / (ms * 1e-3)
     e2e_v = total_iters / (ms_e2e * 1e-3)
     peak, peak_src = peaks()
     dom = max((k for k in stage_ms if k not in ("pose_begin", "pose_finish", "tile_scan")), key=lambda k: stage_ms[k])
-    ab = algorithmic_bytes(dom, 1, N, M, P, T)
+    ab = algorithmic_bytes(dom, Cn, N, M, P * Cn, T * Cn)
     ach = ab / (stage_ms[dom] * 1e-3) / 1e9
     sum_ms = sum(stage_ms.values())
     stages = {k: {"ms": round(v, 5), "share": round(v / sum_ms, 4),
-                  "alg_GBps": round(algorithmic_bytes(k, 1, N, M, P, T) / (v * 1e-3) / 1e9, 1) if v > 0 else None}
+                  "alg_GBps": round(algorithmic_bytes(k, Cn, N, M, P * Cn, T * Cn) / (v * 1e-3) / 1e9, 1) if v > 0 else None}
               for k, v in stage_ms.items()}
-    iter_bytes = sum(algorithmic_bytes(k, 1, N, M, P, T) for k in stage_ms)
+    iter_bytes = sum(algorithmic_bytes(k, Cn, N, M, P * Cn, T * Cn) for k in stage_ms)
     out = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W_,
         "ms_per_step": round(ms / K, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {fp0.W}x{fp0.H}, N={N} Gaussians, M={M} tile intersections, "
                                f"{iters}-iteration pose optimisation per step (BASELINE.json configs[1])",
-                   "iters_per_step": iters, "gaussians": N, "isects": M, "pixels": P, "tiles": T,
+                   "iters_per_step": iters, "hypotheses": Cn, "depth_lambda": args.depth_lambda,
+                   "normal_lambda": args.normal_lambda, "gaussians": N, "isects": M, "pixels": P, "tiles": T,
                    "frames_per_rank": n_pool, "sharding": "independent frames per rank, final all_gather of pose errors",
                    "l2": f"inputs larger than L2: {n_pool} frames x ~{round((44*N + 24*P + 12*M + 40*N) / 1e6)} MB of "
                          "buffers cycled between steps; iterations inside a step reuse L2 as the real loop does",
@@ -344,6 +365,9 @@ def main():
     ap.add_argument("--iters", type=int, default=100, help="pose iterations per step (frame)")
     ap.add_argument("--max-steps", type=int, default=2000, help="LR schedule horizon (GsplatLoc_eval.py --num-iters)")
     ap.add_argument("--pool", type=int, default=4, help="distinct frames cycled per rank")
+    ap.add_argument("--cameras", type=int, default=1, help="pose hypotheses per frame (BASELINE.json configs[3]: 64)")
+    ap.add_argument("--depth-lambda", type=float, default=0.8)
+    ap.add_argument("--normal-lambda", type=float, default=0.0)
     ap.add_argument("--cpu-iters", type=int, default=2)
     ap.add_argument("--ref-max-steps", type=int, default=6)
     ap.add_argument("--no-cpu-baseline", action="store_true")
