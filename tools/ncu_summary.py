@@ -31,6 +31,7 @@ KEYS = [
     ("sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", "xu%"),
     ("sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", "lsu%"),
     ("l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "smem_wavefronts"),
+    ("lts__t_sectors.sum", "l2_MB"),   # 32-byte sectors through L2 (lts__t_bytes is not in --set full)
     ("sm__warps_active.avg.pct_of_peak_sustained_active", "occ%"),
     ("launch__registers_per_thread", "regs"),
     ("launch__shared_mem_per_block_static", "smem_static"),
@@ -82,6 +83,8 @@ def main():
                     cells.append(f"{to_us(v, u):.1f} us")
                 elif lab.startswith("dram_"):
                     cells.append(f"{to_bytes(v, u) / 1e6:.2f} MB")
+                elif lab == "l2_MB":
+                    cells.append(f"{float(v) * 32 / 1e6:.1f}")
                 elif lab in ("warp_inst", "smem_wavefronts"):
                     cells.append(f"{float(v) / 1e6:.1f} M")
                 elif lab.endswith("%") or lab == "thr/inst":
