@@ -114,3 +114,31 @@ def test_geometry_fails_loudly_without_cuda(geo):
         geo.knn(torch.zeros(4, 3), 2)
     with pytest.raises(RuntimeError):
         geo.knn(torch.zeros(4, 3).cuda(), 64)
+
+
+def test_per_frame_setup_on_the_gpu_reproduces_the_host_pipeline(geo):
+    """tools/track_sequence.py's per-frame setup (depth image -> world lattice -> KNN scales -> GT re-render), all on
+    the GPU, against the synthetic generator's numpy / cKDTree pipeline and the rasteriser oracle's re-render."""
+    from gsplatloc_b200 import synthetic as syn
+    cam = U.SMALL_CAM
+    rng = np.random.default_rng(5)
+    scene = syn.make_scene(rng)
+    A = syn.make_pose(rng)
+    K = np.array([[cam["fx"], 0, cam["cx"]], [0, cam["fy"], cam["cy"]], [0, 0, 1]], dtype=np.float64)
+    W, H, s = cam["W"], cam["H"], 2
+    dA = syn.raycast_depth(scene, A, K, W, H)
+    pts_ref = syn.backproject(dA, K, A, s)
+    pts = geo.depth_to_points(torch.tensor(dA).cuda(), torch.tensor(K, dtype=torch.float32),
+                              c2w=torch.tensor(A, dtype=torch.float32))
+    pts = pts.view(H, W, 3)[s // 2::s, s // 2::s].reshape(-1, 3).contiguous()
+    assert U.rel_err(pts.cpu().numpy(), pts_ref) < 1e-6
+    sc = geo.init_gs_scales(pts, 5, reference_faithful=False).cpu().numpy()
+    assert U.rel_err(sc, syn.knn_scales(pts_ref)) < 1e-4
+    # GT re-render of the frame's own lattice from its own viewpoint (camera frame, identity pose)
+    cam_pts = geo.depth_to_points(torch.tensor(dA).cuda(), torch.tensor(K, dtype=torch.float32))
+    cam_pts = cam_pts.view(H, W, 3)[s // 2::s, s // 2::s].reshape(-1, 3).contiguous()
+    d = geo.compute_depth_gt(cam_pts, None, torch.tensor(K, dtype=torch.float32)[None].cuda(), torch.eye(4)[None].cuda(),
+                             H, W, reference_faithful=False).cpu().numpy()
+    ref = geo_o.compute_depth_gt(cam_pts.cpu().numpy(), K, np.eye(4), H, W, reference_faithful=False)
+    err = np.abs(d - ref) / np.maximum(np.abs(ref), 1e-6)
+    assert np.mean(err > 1e-4) < 1e-3, float(np.mean(err > 1e-4))
