@@ -78,6 +78,7 @@ void launch_loss(int C, int W, int H, const float* ed, const float* alpha, const
 
 // ---- pose.cu
 void launch_pose_begin(int C, const gsb_pose_state* state, float* viewmats, cudaStream_t st);
+int raster_bwd_partials_per_tile();
 void launch_pose_finish(int C, int n_tiles, int n_loss_blocks, const float* partials, const float* loss_partials,
                         float* viewmats, gsb_pose_state* state, int* stop, gsb_tracker_config cfg,
                         float inv_pixels, float inv_rows3, float* history, int history_cap, cudaStream_t st);

@@ -294,11 +294,16 @@ struct QuadScratch {
 };
 
 #define GSB_NEG_LOG2E -1.4426950408889634f
+#ifndef GSB_BWD_WARPS
+#define GSB_BWD_WARPS 4   // warps (8x4 patches) per block: 8 = one block per tile, 4 = two blocks per tile (finer
+#endif                    // block scheduling: a block's slot is freed when its slowest warp ends, and the last wave is shorter)
 #ifndef GSB_BWD_OCC
-#define GSB_BWD_OCC 2   // resident blocks per SM the quad kernel is compiled for (128 registers)
+#define GSB_BWD_OCC (16 / GSB_BWD_WARPS)   // resident blocks per SM the quad kernel is compiled for (128 registers)
 #endif
+#define GSB_BWD_THREADS (32 * GSB_BWD_WARPS)
+#define GSB_BWD_SPLIT (8 / GSB_BWD_WARPS)    // blocks per tile
 
-__global__ void __launch_bounds__(256, GSB_BWD_OCC) raster_bwd_quad_kernel(
+__global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad_kernel(
     int C, int N, int W, int H, int tile_w, int tile_h, const float4* __restrict__ rec,
     const int* __restrict__ tile_offsets, const int* __restrict__ n_isects_dev, const int* __restrict__ flatten_ids,
     const float* __restrict__ render_alphas, const int* __restrict__ last_ids, const float* __restrict__ v_depth,
@@ -306,19 +311,21 @@ __global__ void __launch_bounds__(256, GSB_BWD_OCC) raster_bwd_quad_kernel(
     const float* __restrict__ scales, const float* __restrict__ viewmats, const float* __restrict__ Ks, float eps2d,
     float* __restrict__ partials, const int* __restrict__ stop, const unsigned char* __restrict__ masks,
     const int* __restrict__ iso_flag) {
-    __shared__ QuadScratch s_w[8];
-    __shared__ float s_pose[12 * 256];
+    __shared__ QuadScratch s_w[GSB_BWD_WARPS];
+    __shared__ float s_pose[12 * GSB_BWD_THREADS];
     __shared__ LiftCtx s_ctx;
 
     const int cam = blockIdx.z;
     if (stop && stop[cam]) return;
-    const int tile_id = blockIdx.y * tile_w + blockIdx.x;
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int tile_x = blockIdx.x / GSB_BWD_SPLIT, part = blockIdx.x % GSB_BWD_SPLIT;
+    const int tile_id = blockIdx.y * tile_w + tile_x;
+    const int tid = threadIdx.x, lane = tid & 31, lwid = tid >> 5;
+    const int wid = lwid + part * GSB_BWD_WARPS;                  // patch index inside the tile (bit of the patch masks)
     const int gq = lane & 3, pr = lane >> 2;
-    const int j = blockIdx.x * 16 + (wid & 1) * 8 + pr;          // this lane's pixel column
+    const int j = tile_x * 16 + (wid & 1) * 8 + pr;               // this lane's pixel column
     const int i0 = blockIdx.y * 16 + (wid >> 1) * 4;              // first row of the patch
     const float px = (float)j + 0.5f, py0 = (float)i0 + 0.5f;
-    const float tile_x0 = (float)(blockIdx.x * 16), tile_y0 = (float)(blockIdx.y * 16);
+    const float tile_x0 = (float)(tile_x * 16), tile_y0 = (float)(blockIdx.y * 16);
     const int bin = cam * tile_w * tile_h + tile_id;
     const int range_start = tile_offsets[bin];
     const int range_end = (bin == C * tile_w * tile_h - 1) ? *n_isects_dev : tile_offsets[bin + 1];
@@ -330,7 +337,7 @@ __global__ void __launch_bounds__(256, GSB_BWD_OCC) raster_bwd_quad_kernel(
         s_ctx.iso = iso_flag ? *iso_flag : 0;
     }
 #pragma unroll
-    for (int k = 0; k < 12; ++k) s_pose[k * 256 + tid] = 0.f;
+    for (int k = 0; k < 12; ++k) s_pose[k * GSB_BWD_THREADS + tid] = 0.f;
     __syncthreads();
 
     // state of the lane's four pixels (replicated in the four lanes of a column)
@@ -352,7 +359,7 @@ __global__ void __launch_bounds__(256, GSB_BWD_OCC) raster_bwd_quad_kernel(
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) warp_bin_final = max(warp_bin_final, __shfl_xor_sync(0xffffffffu, warp_bin_final, o));
 
-    QuadScratch& ws = s_w[wid];
+    QuadScratch& ws = s_w[lwid];
     float* const pose_col = s_pose + tid;
     int r_head = 0, r_tail = 0;   // compaction ring (uniform)
     int q_head = 0, q_tail = 0;   // lift ring (uniform)
@@ -488,7 +495,7 @@ __global__ void __launch_bounds__(256, GSB_BWD_OCC) raster_bwd_quad_kernel(
                 const int gid = ws.qid[slot];
                 if (gid >= 0)
                     lift_to_pose(&s_ctx, gid, ws.qsum[slot][0], ws.qsum[slot][1], ws.qsum[slot][2], ws.qsum[slot][3],
-                                 ws.qsum[slot][4], ws.qsum[slot][5], pose_col, 256);
+                                 ws.qsum[slot][4], ws.qsum[slot][5], pose_col, GSB_BWD_THREADS);
                 q_head += 32;
                 __syncwarp();
             }
@@ -500,15 +507,15 @@ __global__ void __launch_bounds__(256, GSB_BWD_OCC) raster_bwd_quad_kernel(
         const int gid = ws.qid[slot];
         if (gid >= 0)
             lift_to_pose(&s_ctx, gid, ws.qsum[slot][0], ws.qsum[slot][1], ws.qsum[slot][2], ws.qsum[slot][3],
-                         ws.qsum[slot][4], ws.qsum[slot][5], pose_col, 256);
+                         ws.qsum[slot][4], ws.qsum[slot][5], pose_col, GSB_BWD_THREADS);
     }
     __syncthreads();
-    for (int k = wid; k < 12; k += 8) {
+    for (int k = lwid; k < 12; k += GSB_BWD_WARPS) {
         float s = 0.f;
 #pragma unroll
-        for (int q = 0; q < 8; ++q) s += s_pose[k * 256 + q * 32 + lane];
+        for (int q = 0; q < GSB_BWD_WARPS; ++q) s += s_pose[k * GSB_BWD_THREADS + q * 32 + lane];
         s = warp_sum(s);
-        if (lane == 0) partials[(size_t)bin * 12 + k] = s;
+        if (lane == 0) partials[((size_t)bin * GSB_BWD_SPLIT + part) * 12 + k] = s;
     }
 }
 
@@ -519,8 +526,8 @@ void launch_raster_bwd_lift(int C, int N, int W, int H, int tile_w, int tile_h, 
                             const float* viewmats, const float* Ks, float eps2d, float* partials, const int* stop,
                             const unsigned char* masks, const int* iso_flag, cudaStream_t st) {
     if (C * tile_w * tile_h == 0) return;
-    dim3 grid(tile_w, tile_h, C);
-    raster_bwd_quad_kernel<<<grid, 256, 0, st>>>(C, N, W, H, tile_w, tile_h, rec, tile_offsets, n_isects_dev,
+    dim3 grid(tile_w * GSB_BWD_SPLIT, tile_h, C);
+    raster_bwd_quad_kernel<<<grid, GSB_BWD_THREADS, 0, st>>>(C, N, W, H, tile_w, tile_h, rec, tile_offsets, n_isects_dev,
                                                  flatten_ids, render_alphas, last_ids, v_depth, v_alpha, means, quats,
                                                  scales, viewmats, Ks, eps2d, partials, stop, masks, iso_flag);
 }
@@ -559,5 +566,8 @@ void launch_map_iso(int N, const float* scales, int* flag, cudaStream_t st) {
     map_iso_init_kernel<<<1, 1, 0, st>>>(flag);
     if (N > 0) map_iso_kernel<<<(N + 255) / 256, 256, 0, st>>>(N, scales, flag);
 }
+
+// 12-float partials the lifted backward writes per (camera, tile)
+int raster_bwd_partials_per_tile() { return GSB_BWD_SPLIT; }
 
 }  // namespace gsb

@@ -101,7 +101,7 @@ static void enqueue_iteration(gsb_tracker* t, bool forward_only, cudaEvent_t* ma
                            t->alpha, t->last_ids, t->v_depth, t->v_alpha, t->means, t->quats, t->scales, t->viewmats,
                            t->Ks, c.eps2d, t->partials, t->stop, t->masks, t->iso_flag, st);
     GSB_MARK();
-    launch_pose_finish(C, t->n_tiles, t->n_loss_blocks, t->partials, t->loss_partials, t->viewmats, t->state, t->stop,
+    launch_pose_finish(C, t->n_tiles * raster_bwd_partials_per_tile(), t->n_loss_blocks, t->partials, t->loss_partials, t->viewmats, t->state, t->stop,
                        c, inv_p, 1.f / (3.f * (float)t->H), t->history, t->history_cap, st);
     GSB_MARK();
 #undef GSB_MARK
@@ -202,7 +202,7 @@ int gsb_tracker_create(gsb_tracker** out, int C, int W, int H, void* stream) {
     TCK(cudaMalloc(&t->v_depth, sizeof(float) * P), "alloc");
     TCK(cudaMalloc(&t->v_alpha, sizeof(float) * P), "alloc");
     TCK(cudaMalloc(&t->last_ids, sizeof(int) * P), "alloc");
-    TCK(cudaMalloc(&t->partials, sizeof(float) * nb * 12), "alloc");
+    TCK(cudaMalloc(&t->partials, sizeof(float) * nb * 12 * raster_bwd_partials_per_tile()), "alloc");
     TCK(cudaMalloc(&t->loss_partials, sizeof(float) * (size_t)C * t->n_loss_blocks * 3), "alloc");
     TCK(cudaMalloc(&t->normal_rows, sizeof(float) * (size_t)C * H * 9), "alloc");
     TCK(cudaMalloc(&t->history, sizeof(float) * (size_t)t->history_cap * C * 8), "alloc");
@@ -210,7 +210,7 @@ int gsb_tracker_create(gsb_tracker** out, int C, int W, int H, void* stream) {
     TCK(cudaMemsetAsync(t->counts, 0, sizeof(int) * nb, t->stream), "memset");
     TCK(cudaMemsetAsync(t->stop, 0, sizeof(int) * C, t->stream), "memset");
     TCK(cudaMemsetAsync(t->n_isects, 0, sizeof(int) * 3, t->stream), "memset");
-    TCK(cudaMemsetAsync(t->partials, 0, sizeof(float) * nb * 12, t->stream), "memset");
+    TCK(cudaMemsetAsync(t->partials, 0, sizeof(float) * nb * 12 * raster_bwd_partials_per_tile(), t->stream), "memset");
     TCK(cudaEventCreate(&t->ev0), "event");
     TCK(cudaEventCreate(&t->ev1), "event");
     *out = t;
