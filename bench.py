@@ -108,9 +108,10 @@ def make_frames(workload: str, n: int, seed0: int):
 def algorithmic_bytes(stage: str, C: int, N: int, M: int, P: int, T: int) -> float:
     """SURVEY.md §8(d) per-unit figures (fp32, ED-only, pose-gradient-only) x the units one launch processes."""
     return {
-        "project_bin": C * N * (40 + 28) + C * N * (12 + 4),       # proj_fwd + the count half of isect
-        "tile_scan": 12.0 * T,
-        "bin_emit": C * N * (16 + 8) + 12.0 * M,                   # emit reads + key/value write
+        # proj_fwd + the whole of isect's count / scan / emit (one fused pass into fixed-capacity tile bins)
+        "project_bin": C * N * (40 + 28) + C * N * (12 + 4) + 12.0 * T + C * N * (16 + 8) + 12.0 * M,
+        "tile_scan": 0.0,                                          # fused away (slot kept for the stage table)
+        "bin_emit": 0.0,
         "tile_sort": 8.0 * M + 12.0 * M,                           # one read of the keys, one write of ids (+offsets)
         "raster_fwd": 32.0 * M + 12.0 * P,
         "loss": 20.0 * P,

@@ -458,6 +458,62 @@ __global__ void __launch_bounds__(256) tile_sort_kernel(int n_tiles, int tile_bi
     }
 }
 
+// Fixed-capacity bins (tracker path, filled by project_emit_kernel): bin b owns keys[b * tile_cap ...], cursor[b] is its
+// fill level.  Sorts the bin, publishes its range (ranges[b] = {start, start + n}: what isect_offsets[b], [b + 1] are in
+// the compact layout), re-zeroes the cursor for the next iteration and adds n to the intersection counter.
+__global__ void __launch_bounds__(256) tile_sort_fixed_kernel(int n_tiles, int tile_cap, int* __restrict__ cursor,
+                                                              uint64_t* __restrict__ keys,
+                                                              int* __restrict__ flatten_ids, int2* __restrict__ ranges,
+                                                              int* __restrict__ n_isects,
+                                                              const int* __restrict__ stop) {
+    __shared__ uint64_t sk[SORT_SMEM];
+    const int bin = blockIdx.x;
+    const int cam = bin / n_tiles;
+    if (stop && stop[cam]) return;
+    const int n = min(cursor[bin], tile_cap);
+    const int start = bin * tile_cap;
+    __syncthreads();   // every thread has read the fill level before it is cleared
+    if (threadIdx.x == 0) {
+        ranges[bin] = make_int2(start, start + n);
+        cursor[bin] = 0;
+        if (n > 0) atomicAdd(n_isects, n);
+    }
+    if (n <= 0) return;
+    uint64_t* g = keys + start;
+    if (n <= 512) { reg_tile_sort<2>(g, n, sk, start, flatten_ids, nullptr, 0); return; }
+    if (n <= 1024) { reg_tile_sort<4>(g, n, sk, start, flatten_ids, nullptr, 0); return; }
+    uint64_t* a = g;
+    if (n <= SORT_SMEM) {
+        for (int i = threadIdx.x; i < n; i += blockDim.x) sk[i] = g[i];
+        a = sk;
+    }
+    __syncthreads();
+    bitonic_sort(a, n, n <= SORT_SMEM);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) flatten_ids[start + i] = (int)(uint32_t)a[i];
+}
+
+// Debug / parity aid: fixed-capacity bins -> gsplat's compact layout (flatten_ids[M], given compact offsets).
+__global__ void __launch_bounds__(256) compact_bins_kernel(const int2* __restrict__ ranges,
+                                                           const int* __restrict__ padded,
+                                                           const int* __restrict__ offsets, int* __restrict__ out) {
+    const int2 r = ranges[blockIdx.x];
+    const int dst = offsets[blockIdx.x];
+    for (int i = threadIdx.x; i < r.y - r.x; i += blockDim.x) out[dst + i] = padded[r.x + i];
+}
+
+void launch_tile_sort_fixed(int C, int n_tiles, int tile_cap, int* cursor, uint64_t* keys, int* flatten_ids,
+                            int2* ranges, int* n_isects, const int* stop, cudaStream_t st) {
+    if (C * n_tiles == 0) return;
+    tile_sort_fixed_kernel<<<C * n_tiles, 256, 0, st>>>(n_tiles, tile_cap, cursor, keys, flatten_ids, ranges, n_isects,
+                                                        stop);
+}
+
+void launch_compact_bins(int n_bins, const int2* ranges, const int* padded, const int* offsets, int* out,
+                         cudaStream_t st) {
+    if (n_bins == 0) return;
+    compact_bins_kernel<<<n_bins, 256, 0, st>>>(ranges, padded, offsets, out);
+}
+
 void launch_tile_hist(int CN, int N, const float* means2d, const int* radii, int tile_size, int tile_w, int tile_h,
                       int* tiles_per_gauss, int* counts, cudaStream_t st) {
     if (CN == 0) return;

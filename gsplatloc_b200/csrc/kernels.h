@@ -22,6 +22,12 @@ void launch_project_bin(int C, int N, const float* means, const float* quats, co
                         int tile_h, float eps2d, float near_plane, float far_plane, float radius_clip, float4* rec,
                         uint2* bbox, int* counts, const int* stop, cudaStream_t st);
 
+void launch_project_emit(int C, int N, const float* means, const float* quats, const float* scales,
+                         const float* opacities, const float* viewmats, const float* Ks, int W, int H, int tile_w,
+                         int tile_h, float eps2d, float near_plane, float far_plane, float radius_clip, float4* rec,
+                         int* cursor, uint64_t* keys, int tile_cap, int* n_isects, int* overflow, const int* stop,
+                         cudaStream_t st);
+
 // ---- isect.cu
 void launch_isect_count(int CN, const float* means2d, const int* radii, int tile_size, int tile_w, int tile_h,
                         int* tiles_per_gauss, cudaStream_t st);
@@ -47,9 +53,14 @@ void launch_bin_emit_soa(int CN, int N, const float* means2d, const int* radii, 
 void launch_tile_sort(int C, int n_tiles, int tile_bits, const int* offsets, uint64_t* keys, int* flatten_ids,
                       int64_t* isect_ids, int cap, const int* stop, cudaStream_t st);
 
+void launch_tile_sort_fixed(int C, int n_tiles, int tile_cap, int* cursor, uint64_t* keys, int* flatten_ids,
+                            int2* ranges, int* n_isects, const int* stop, cudaStream_t st);
+void launch_compact_bins(int n_bins, const int2* ranges, const int* padded, const int* offsets, int* out,
+                         cudaStream_t st);
+
 // ---- raster_fwd.cu / raster_bwd.cu
-void launch_raster_fwd_packed(int C, int W, int H, int tile_w, int tile_h, const float4* rec, const int* tile_offsets,
-                              const int* n_isects_dev, const int* flatten_ids, float* render_depth,
+void launch_raster_fwd_packed(int C, int W, int H, int tile_w, int tile_h, const float4* rec, const int2* ranges,
+                              const int* flatten_ids, float* render_depth,
                               float* render_alphas, int* last_ids, int normalize, const int* stop,
                               unsigned char* masks_out, cudaStream_t st);
 int launch_raster_fwd_soa(int cdim, int C, int W, int H, int tile_w, int tile_h, const float* means2d,
@@ -57,7 +68,7 @@ int launch_raster_fwd_soa(int cdim, int C, int W, int H, int tile_w, int tile_h,
                           const int* tile_offsets, int n_isects, const int* flatten_ids, float* render_colors,
                           float* render_alphas, int* last_ids, cudaStream_t st);
 void launch_raster_bwd_lift(int C, int N, int W, int H, int tile_w, int tile_h, const float4* rec,
-                            const int* tile_offsets, const int* n_isects_dev, const int* flatten_ids,
+                            const int2* ranges, const int* flatten_ids,
                             const float* render_alphas, const int* last_ids, const float* v_depth,
                             const float* v_alpha, const float* means, const float* quats, const float* scales,
                             const float* viewmats, const float* Ks, float eps2d, float* partials, const int* stop,

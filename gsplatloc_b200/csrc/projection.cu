@@ -191,6 +191,119 @@ void launch_project_bwd(int C, int N, const float* means, const float* quats, co
                                              v_depths, v_conics, v_means, v_quats, v_scales, v_viewmats);
 }
 
+// Tracker fast path, single pass: projection AND scatter of the (depth bits << 32 | flat index) keys into per-tile
+// bins of FIXED capacity ``tile_cap`` (bin b owns keys[b * tile_cap, (b + 1) * tile_cap)), so that neither a histogram
+// pass nor a scan nor a second pass over the Gaussians is needed: cursor[b] (zero at entry, re-zeroed by tile_sort) is
+// the fill level.  Same warp-aggregated atomics as bin_emit_kernel (isect.cu): lanes with the same tile box vote, the
+// group's leader reserves room once per tile; boxes larger than 2 x 2 tiles are flattened over the warp.  A bin that
+// would overflow raises *overflow (the run is reported invalid and re-sized, tracker.cu).  Thread (0,0) clears the
+// intersection counter that tile_sort accumulates.
+__global__ void __launch_bounds__(256) project_emit_kernel(
+    int C, int N, const float* __restrict__ means, const float* __restrict__ quats, const float* __restrict__ scales,
+    const float* __restrict__ opacities, const float* __restrict__ viewmats, const float* __restrict__ Ks, int W, int H,
+    int tile_w, int tile_h, float eps2d, float near_plane, float far_plane, float radius_clip,
+    float4* __restrict__ rec, int* __restrict__ cursor, uint64_t* __restrict__ keys, int tile_cap,
+    int* __restrict__ n_isects, int* __restrict__ overflow, const int* __restrict__ stop) {
+    __shared__ int s_incl[8][32];
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    const int c = blockIdx.y;
+    if (n == 0 && c == 0) *n_isects = 0;
+    if (stop && stop[c]) return;   // uniform over the block
+    const int lane = threadIdx.x & 31;
+    uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0;
+    float depth = 0.f;
+    bool live = false;
+    const size_t i = (size_t)c * N + (n < N ? n : 0);
+    if (n < N) {
+        Cam cam = load_cam(viewmats + c * 16, Ks + c * 9);
+        GaussIn g = load_gauss(means, quats, scales, n);
+        Proj p; float S[6], Sc[6];
+        const bool ok = project_gaussian(cam, g.mean, g.q, g.s, W, H, eps2d, near_plane, far_plane, radius_clip, p, S, Sc);
+        if (ok) {
+            tile_bbox(p.mx, p.my, p.radius, GSB_TILE, tile_w, tile_h, x0, y0, x1, y1);
+            rec[2 * i] = make_float4(p.mx, p.my, p.pz, opacities[n]);
+            rec[2 * i + 1] = make_float4(p.ca, p.cb, p.cc, __int_as_float(p.radius));
+            depth = p.pz;
+            live = x1 > x0 && y1 > y0;
+        } else {
+            rec[2 * i + 1] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
+        }
+    }
+    const uint32_t bw = x1 - x0, bh = y1 - y0;
+    const bool small = live && bw <= 2 && bh <= 2;
+    const uint64_t key = ((uint64_t)(uint32_t)__float_as_int(depth) << 32) | (uint32_t)i;
+    int* cur = cursor + (size_t)c * tile_w * tile_h;
+    uint64_t* kbase = keys + (size_t)c * tile_w * tile_h * tile_cap;
+    bool over = false;
+    const unsigned grp = __match_any_sync(0xffffffffu, small ? (x0 | (x1 << 16)) : 0u) &
+                         __match_any_sync(0xffffffffu, small ? (y0 | (y1 << 16)) : 0u);
+    if (small) {
+        const int leader = __ffs(grp) - 1, cnt = __popc(grp), rank = __popc(grp & ((1u << lane) - 1u));
+        const int t00 = y0 * tile_w + x0;
+        const bool hx = bw > 1, hy = bh > 1;
+        int b0 = 0, b1 = 0, b2 = 0, b3 = 0;
+        if (lane == leader) {
+            b0 = atomicAdd(cur + t00, cnt);
+            if (hx) b1 = atomicAdd(cur + t00 + 1, cnt);
+            if (hy) b2 = atomicAdd(cur + t00 + tile_w, cnt);
+            if (hx && hy) b3 = atomicAdd(cur + t00 + tile_w + 1, cnt);
+        }
+        b0 = __shfl_sync(grp, b0, leader) + rank; b1 = __shfl_sync(grp, b1, leader) + rank;
+        b2 = __shfl_sync(grp, b2, leader) + rank; b3 = __shfl_sync(grp, b3, leader) + rank;
+        if (b0 < tile_cap) kbase[(size_t)t00 * tile_cap + b0] = key; else over = true;
+        if (hx) { if (b1 < tile_cap) kbase[(size_t)(t00 + 1) * tile_cap + b1] = key; else over = true; }
+        if (hy) { if (b2 < tile_cap) kbase[(size_t)(t00 + tile_w) * tile_cap + b2] = key; else over = true; }
+        if (hx && hy) { if (b3 < tile_cap) kbase[(size_t)(t00 + tile_w + 1) * tile_cap + b3] = key; else over = true; }
+    }
+    // larger boxes: (Gaussian, tile) pairs flattened over the warp, 32 per round
+    const int mine = (live && !small) ? (int)(bw * bh) : 0;
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int up = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += up;
+    }
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    if (total > 0) {
+        int* wincl = s_incl[threadIdx.x >> 5];
+        wincl[lane] = incl;
+        __syncwarp();
+        const int excl = incl - mine;
+        const uint32_t key_hi = (uint32_t)__float_as_int(depth);
+        for (int w0 = 0; w0 < total; w0 += 32) {
+            const int w = w0 + lane;
+            int src = 0;   // the first lane whose inclusive sum exceeds w
+#pragma unroll
+            for (int step = 16; step > 0; step >>= 1)
+                if (wincl[src + step - 1] <= w) src += step;
+            src = min(src, 31);
+            const uint32_t sx0 = __shfl_sync(0xffffffffu, x0, src), sy0 = __shfl_sync(0xffffffffu, y0, src);
+            const uint32_t sbw = __shfl_sync(0xffffffffu, bw, src);
+            const int sexcl = __shfl_sync(0xffffffffu, excl, src);
+            const uint32_t shi = __shfl_sync(0xffffffffu, key_hi, src), slo = __shfl_sync(0xffffffffu, (uint32_t)i, src);
+            if (w < total) {
+                const uint32_t t = (uint32_t)(w - sexcl);
+                const int tile = (int)((sy0 + t / sbw) * tile_w + sx0 + t % sbw);
+                const int pos = atomicAdd(cur + tile, 1);
+                if (pos < tile_cap) kbase[(size_t)tile * tile_cap + pos] = ((uint64_t)shi << 32) | slo; else over = true;
+            }
+        }
+    }
+    if (over) *overflow = 1;
+}
+
+void launch_project_emit(int C, int N, const float* means, const float* quats, const float* scales,
+                         const float* opacities, const float* viewmats, const float* Ks, int W, int H, int tile_w,
+                         int tile_h, float eps2d, float near_plane, float far_plane, float radius_clip, float4* rec,
+                         int* cursor, uint64_t* keys, int tile_cap, int* n_isects, int* overflow, const int* stop,
+                         cudaStream_t st) {
+    if (N == 0 || C == 0) return;
+    dim3 grid((N + 255) / 256, C);
+    project_emit_kernel<<<grid, 256, 0, st>>>(C, N, means, quats, scales, opacities, viewmats, Ks, W, H, tile_w, tile_h,
+                                              eps2d, near_plane, far_plane, radius_clip, rec, cursor, keys, tile_cap,
+                                              n_isects, overflow, stop);
+}
+
 void launch_project_bin(int C, int N, const float* means, const float* quats, const float* scales,
                         const float* opacities, const float* viewmats, const float* Ks, int W, int H, int tile_w,
                         int tile_h, float eps2d, float near_plane, float far_plane, float radius_clip, float4* rec,

@@ -305,7 +305,7 @@ struct QuadScratch {
 
 __global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad_kernel(
     int C, int N, int W, int H, int tile_w, int tile_h, const float4* __restrict__ rec,
-    const int* __restrict__ tile_offsets, const int* __restrict__ n_isects_dev, const int* __restrict__ flatten_ids,
+    const int2* __restrict__ ranges, const int* __restrict__ flatten_ids,
     const float* __restrict__ render_alphas, const int* __restrict__ last_ids, const float* __restrict__ v_depth,
     const float* __restrict__ v_alpha_img, const float* __restrict__ means, const float* __restrict__ quats,
     const float* __restrict__ scales, const float* __restrict__ viewmats, const float* __restrict__ Ks, float eps2d,
@@ -327,8 +327,8 @@ __global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad_
     const float px = (float)j + 0.5f, py0 = (float)i0 + 0.5f;
     const float tile_x0 = (float)(tile_x * 16), tile_y0 = (float)(blockIdx.y * 16);
     const int bin = cam * tile_w * tile_h + tile_id;
-    const int range_start = tile_offsets[bin];
-    const int range_end = (bin == C * tile_w * tile_h - 1) ? *n_isects_dev : tile_offsets[bin + 1];
+    const int2 range = ranges[bin];   // fixed-capacity bin of this tile (tile_sort_fixed_kernel)
+    const int range_start = range.x, range_end = range.y;
 
     if (tid == 0) {
         s_ctx.cam = load_cam(viewmats + cam * 16, Ks + cam * 9);
@@ -520,14 +520,14 @@ __global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad_
 }
 
 void launch_raster_bwd_lift(int C, int N, int W, int H, int tile_w, int tile_h, const float4* rec,
-                            const int* tile_offsets, const int* n_isects_dev, const int* flatten_ids,
+                            const int2* ranges, const int* flatten_ids,
                             const float* render_alphas, const int* last_ids, const float* v_depth,
                             const float* v_alpha, const float* means, const float* quats, const float* scales,
                             const float* viewmats, const float* Ks, float eps2d, float* partials, const int* stop,
                             const unsigned char* masks, const int* iso_flag, cudaStream_t st) {
     if (C * tile_w * tile_h == 0) return;
     dim3 grid(tile_w * GSB_BWD_SPLIT, tile_h, C);
-    raster_bwd_quad_kernel<<<grid, GSB_BWD_THREADS, 0, st>>>(C, N, W, H, tile_w, tile_h, rec, tile_offsets, n_isects_dev,
+    raster_bwd_quad_kernel<<<grid, GSB_BWD_THREADS, 0, st>>>(C, N, W, H, tile_w, tile_h, rec, ranges,
                                                  flatten_ids, render_alphas, last_ids, v_depth, v_alpha, means, quats,
                                                  scales, viewmats, Ks, eps2d, partials, stop, masks, iso_flag);
 }

@@ -53,7 +53,7 @@ __global__ void __launch_bounds__(256) raster_fwd_kernel(
     const float* __restrict__ backgrounds, const int* __restrict__ tile_offsets, const int* __restrict__ n_isects_dev,
     int n_isects_host, const int* __restrict__ flatten_ids, float* __restrict__ render_colors,
     float* __restrict__ render_alphas, int* __restrict__ last_ids, int normalize_last, const int* __restrict__ stop,
-    unsigned char* __restrict__ masks_out) {
+    unsigned char* __restrict__ masks_out, const int2* __restrict__ ranges) {
     constexpr int RS = RecStride<CDIM>::value;
     // FB records per staging round: 512 on the tracker path (a depth lattice puts ~300 Gaussians in a tile, so most
     // tiles need ONE round: one barrier pair and one dependent ids -> records load chain instead of two)
@@ -72,8 +72,14 @@ __global__ void __launch_bounds__(256) raster_fwd_kernel(
     bool done = !inside;
     const int n_isects = n_isects_dev ? *n_isects_dev : n_isects_host;
     const int bin = cam * tile_w * tile_h + tile_id;
-    const int range_start = tile_offsets[bin];
-    const int range_end = (bin == C * tile_w * tile_h - 1) ? n_isects : tile_offsets[bin + 1];
+    int range_start, range_end;
+    if (ranges) {   // fixed-capacity bins of the tracker path (tile_sort_fixed_kernel)
+        const int2 r = ranges[bin];
+        range_start = r.x; range_end = r.y;
+    } else {
+        range_start = tile_offsets[bin];
+        range_end = (bin == C * tile_w * tile_h - 1) ? n_isects : tile_offsets[bin + 1];
+    }
     const int num_batches = (range_end - range_start + FB - 1) / FB;
 
     float T = 1.f;
@@ -160,22 +166,21 @@ static void launch_t(int C, int W, int H, int tile_w, int tile_h, const float4* 
                      const float* conics, const float* colors, const float* opacities, const float* backgrounds,
                      const int* tile_offsets, const int* n_isects_dev, int n_isects_host, const int* flatten_ids,
                      float* render_colors, float* render_alphas, int* last_ids, int normalize_last, const int* stop,
-                     unsigned char* masks_out, cudaStream_t st) {
+                     unsigned char* masks_out, const int2* ranges, cudaStream_t st) {
     dim3 grid(tile_w, tile_h, C);
     raster_fwd_kernel<CDIM, PACKED><<<grid, 256, 0, st>>>(C, W, H, tile_w, tile_h, rec, means2d, conics, colors,
                                                             opacities, backgrounds, tile_offsets, n_isects_dev,
                                                             n_isects_host, flatten_ids, render_colors, render_alphas,
-                                                            last_ids, normalize_last, stop, masks_out);
+                                                            last_ids, normalize_last, stop, masks_out, ranges);
 }
 
-void launch_raster_fwd_packed(int C, int W, int H, int tile_w, int tile_h, const float4* rec, const int* tile_offsets,
-                              const int* n_isects_dev, const int* flatten_ids, float* render_depth,
+void launch_raster_fwd_packed(int C, int W, int H, int tile_w, int tile_h, const float4* rec, const int2* ranges,
+                              const int* flatten_ids, float* render_depth,
                               float* render_alphas, int* last_ids, int normalize, const int* stop,
                               unsigned char* masks_out, cudaStream_t st) {
     if (C * tile_w * tile_h == 0) return;
-    launch_t<1, true>(C, W, H, tile_w, tile_h, rec, nullptr, nullptr, nullptr, nullptr, nullptr, tile_offsets,
-                      n_isects_dev, 0, flatten_ids, render_depth, render_alphas, last_ids, normalize, stop, masks_out,
-                      st);
+    launch_t<1, true>(C, W, H, tile_w, tile_h, rec, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0,
+                      flatten_ids, render_depth, render_alphas, last_ids, normalize, stop, masks_out, ranges, st);
 }
 
 int launch_raster_fwd_soa(int cdim, int C, int W, int H, int tile_w, int tile_h, const float* means2d,
@@ -187,7 +192,7 @@ int launch_raster_fwd_soa(int cdim, int C, int W, int H, int tile_w, int tile_h,
     case D:                                                                                                     \
         launch_t<D, false>(C, W, H, tile_w, tile_h, nullptr, means2d, conics, colors, opacities, backgrounds,   \
                            tile_offsets, nullptr, n_isects, flatten_ids, render_colors, render_alphas, last_ids, \
-                           0, nullptr, nullptr, st);                                                            \
+                           0, nullptr, nullptr, nullptr, st);                                                            \
         return 0;
     switch (cdim) {
         GSB_CASE(1) GSB_CASE(2) GSB_CASE(3) GSB_CASE(4) GSB_CASE(5) GSB_CASE(8)

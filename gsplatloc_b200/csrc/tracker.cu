@@ -42,7 +42,9 @@ struct gsb_tracker {
     uint64_t* keys = nullptr;
     int* flatten_ids = nullptr;
     unsigned char* masks = nullptr;   // per tile entry: which 8x4 patches it can reach (written by raster_fwd)
-    int64_t cap = 0;
+    int2* ranges = nullptr;           // per (camera, tile): [start, end) of its sorted entries (fixed-capacity bins)
+    int tile_cap = 0;                 // keys per bin
+    int64_t cap = 0;                  // total = C * tiles * tile_cap
     float *ed = nullptr, *alpha = nullptr, *v_depth = nullptr, *v_alpha = nullptr;
     int* last_ids = nullptr;
     float *partials = nullptr, *loss_partials = nullptr, *normal_rows = nullptr;
@@ -58,9 +60,9 @@ struct gsb_tracker {
     int64_t last_n_isects = 0;
 };
 
-static const int kStages = 9;   // slots of gsb_tracker_profile (slot 0, pose_begin, is fused away and reports 0)
+static const int kStages = 9;   // slots of gsb_tracker_profile; pose_begin, tile_scan and bin_emit are fused away (0)
 static int n_launches_per_iter(const gsb_tracker* t) {
-    return 8 + ((t->cfg.normal_lambda != 0.f && t->cfg.normal_mode == GSB_NORMAL_REFERENCE) ? 1 : 0);
+    return 6 + ((t->cfg.normal_lambda != 0.f && t->cfg.normal_mode == GSB_NORMAL_REFERENCE) ? 1 : 0);
 }
 
 static void invalidate_graph(gsb_tracker* t) {
@@ -78,17 +80,17 @@ static void enqueue_iteration(gsb_tracker* t, bool forward_only, cudaEvent_t* ma
 #define GSB_MARK() do { if (marks) cudaEventRecord(marks[mk++], st); } while (0)
     GSB_MARK();
     GSB_MARK();   // (pose_begin slot: the viewmats are written at set-up by ensure_capacity and afterwards by pose_finish)
-    launch_project_bin(C, N, t->means, t->quats, t->scales, t->opac, t->viewmats, t->Ks, t->W, t->H, t->tile_w,
-                       t->tile_h, c.eps2d, c.near_plane, c.far_plane, c.radius_clip, t->rec, t->bbox, t->counts,
-                       t->stop, st);
+    // projection + scatter into fixed-capacity tile bins in ONE pass (no histogram, scan or second pass)
+    launch_project_emit(C, N, t->means, t->quats, t->scales, t->opac, t->viewmats, t->Ks, t->W, t->H, t->tile_w,
+                        t->tile_h, c.eps2d, c.near_plane, c.far_plane, c.radius_clip, t->rec, t->cursor, t->keys,
+                        t->tile_cap, t->n_isects, t->overflow, t->stop, st);
     GSB_MARK();
-    launch_tile_scan(C * t->n_tiles, t->counts, t->offsets, t->cursor, t->n_isects, (int)t->cap, t->overflow, st);
+    GSB_MARK();   // (tile_scan slot)
+    GSB_MARK();   // (bin_emit slot)
+    launch_tile_sort_fixed(C, t->n_tiles, t->tile_cap, t->cursor, t->keys, t->flatten_ids, t->ranges, t->n_isects,
+                           t->stop, st);
     GSB_MARK();
-    launch_bin_emit_packed(C * N, N, t->rec, t->bbox, t->tile_w, t->tile_h, t->cursor, t->keys, (int)t->cap, t->stop, st);
-    GSB_MARK();
-    launch_tile_sort(C, t->n_tiles, t->tile_bits, t->offsets, t->keys, t->flatten_ids, nullptr, (int)t->cap, t->stop, st);
-    GSB_MARK();
-    launch_raster_fwd_packed(C, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->offsets, t->n_isects, t->flatten_ids,
+    launch_raster_fwd_packed(C, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->ranges, t->flatten_ids,
                              t->ed, t->alpha, t->last_ids, 1, t->stop, t->masks, st);
     GSB_MARK();
     if (forward_only) return;
@@ -97,7 +99,7 @@ static void enqueue_iteration(gsb_tracker* t, bool forward_only, cudaEvent_t* ma
                 (1.f - c.depth_lambda - c.normal_lambda) * inv_p, c.normal_lambda, c.normal_mode, t->Ks,
                 t->normal_rows, 1, t->v_depth, t->v_alpha, t->loss_partials, t->stop, st);
     GSB_MARK();
-    launch_raster_bwd_lift(C, N, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->offsets, t->n_isects, t->flatten_ids,
+    launch_raster_bwd_lift(C, N, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->ranges, t->flatten_ids,
                            t->alpha, t->last_ids, t->v_depth, t->v_alpha, t->means, t->quats, t->scales, t->viewmats,
                            t->Ks, c.eps2d, t->partials, t->stop, t->masks, t->iso_flag, st);
     GSB_MARK();
@@ -116,12 +118,21 @@ static int ensure_capacity(gsb_tracker* t) {
                        t->tile_h, c.eps2d, c.near_plane, c.far_plane, c.radius_clip, t->rec, t->bbox, t->counts,
                        t->stop, st);
     launch_tile_scan(t->C * t->n_tiles, t->counts, t->offsets, t->cursor, t->n_isects, 0x7fffffff, nullptr, st);
-    TCK(cudaMemcpyAsync(t->h_flags + t->C, t->n_isects, sizeof(int), cudaMemcpyDeviceToHost, st), "n_isects d2h");
+    const size_t nb = (size_t)t->C * t->n_tiles;
+    std::vector<int> off(nb + 1);
+    TCK(cudaMemcpyAsync(off.data(), t->offsets, sizeof(int) * (nb + 1), cudaMemcpyDeviceToHost, st), "offsets d2h");
+    TCK(cudaMemsetAsync(t->cursor, 0, sizeof(int) * nb, st), "zero cursors");   // the scan left offsets there
     TCK(cudaStreamSynchronize(st), "capacity pass");
     t->total_launches += 3;
-    int64_t m = t->h_flags[t->C];
-    if (m > t->cap || t->cap == 0) {
-        int64_t want = m + m / 4 + 65536;
+    int fullest = 0;
+    for (size_t b = 0; b < nb; ++b) fullest = std::max(fullest, off[b + 1] - off[b]);
+    // bins are sized for the fullest tile + 25 % + 64 (poses move by centimetres inside a run); a bin that still
+    // overflows raises the flag and the run is repeated with new sizes
+    const int want_cap = ((fullest + fullest / 4 + 64) + 31) & ~31;
+    if (want_cap > t->tile_cap || t->tile_cap == 0) {
+        const int64_t want = (int64_t)nb * want_cap;
+        if (want >= ((int64_t)1 << 31))
+            return fail(GSB_ERR_ARG, "tracker: cameras x tiles x bin capacity exceeds 2^31 entries", cudaSuccess);
         if (t->keys) cudaFree(t->keys);
         if (t->flatten_ids) cudaFree(t->flatten_ids);
         if (t->masks) cudaFree(t->masks);
@@ -130,6 +141,7 @@ static int ensure_capacity(gsb_tracker* t) {
         TCK(cudaMalloc(&t->flatten_ids, sizeof(int) * (size_t)want), "alloc flatten_ids");
         TCK(cudaMalloc(&t->masks, (size_t)want), "alloc masks");
         t->cap = want;
+        t->tile_cap = want_cap;
         invalidate_graph(t);
     }
     t->cap_dirty = false;
@@ -194,6 +206,9 @@ int gsb_tracker_create(gsb_tracker** out, int C, int W, int H, void* stream) {
     TCK(cudaMalloc(&t->counts, sizeof(int) * nb), "alloc");
     TCK(cudaMalloc(&t->offsets, sizeof(int) * (nb + 1)), "alloc");
     TCK(cudaMalloc(&t->cursor, sizeof(int) * nb), "alloc");
+    TCK(cudaMalloc(&t->ranges, sizeof(int2) * nb), "alloc");
+    TCK(cudaMemsetAsync(t->cursor, 0, sizeof(int) * nb, t->stream), "memset");
+    TCK(cudaMemsetAsync(t->ranges, 0, sizeof(int2) * nb, t->stream), "memset");
     TCK(cudaMalloc(&t->n_isects, sizeof(int) * 3), "alloc");
     t->overflow = t->n_isects + 1;
     t->iso_flag = t->n_isects + 2;
@@ -222,7 +237,7 @@ void gsb_tracker_destroy(gsb_tracker* t) {
     cudaStreamSynchronize(t->stream);
     invalidate_graph(t);
     void* bufs[] = {t->means, t->quats, t->scales, t->opac, t->gt, t->Ks, t->viewmats, t->state, t->stop, t->rec,
-                    t->bbox, t->counts, t->offsets, t->cursor, t->n_isects, t->keys, t->flatten_ids, t->masks, t->ed, t->alpha,
+                    t->bbox, t->counts, t->offsets, t->cursor, t->ranges, t->n_isects, t->keys, t->flatten_ids, t->masks, t->ed, t->alpha,
                     t->v_depth, t->v_alpha, t->last_ids, t->partials, t->loss_partials, t->normal_rows,
                     t->history};
     for (void* b : bufs)
@@ -356,7 +371,9 @@ int gsb_tracker_run(gsb_tracker* t, int n_iters, int poll_every, int use_graph, 
     if (t->h_flags[t->C + 1]) {
         t->cap_dirty = true;  // regrow on the next run
         t->cap = 0;
+        t->tile_cap = 0;
         cudaMemsetAsync(t->overflow, 0, sizeof(int), t->stream);
+        cudaMemsetAsync(t->cursor, 0, sizeof(int) * (size_t)t->C * t->n_tiles, t->stream);
         return fail(GSB_ERR_OVERFLOW, "gsb_tracker_run: intersection buffer overflowed; poses must be reset and the run repeated", cudaSuccess);
     }
     return GSB_OK;
@@ -402,7 +419,7 @@ int gsb_tracker_forward(gsb_tracker* t) {
     TCK(cudaMemcpyAsync(t->h_flags + t->C, t->n_isects, sizeof(int) * 2, cudaMemcpyDeviceToHost, t->stream), "flags");
     TCK(cudaStreamSynchronize(t->stream), "forward sync");
     TCK(cudaGetLastError(), "forward");
-    t->total_launches += 5;
+    t->total_launches += 3;
     t->last_n_isects = t->h_flags[t->C];
     return GSB_OK;
 }
@@ -450,10 +467,21 @@ void* gsb_tracker_stream(gsb_tracker* t) { return t ? (void*)t->stream : nullptr
 int gsb_tracker_debug_copy(gsb_tracker* t, int32_t* flatten_ids, int32_t* offsets, float* records) {
     if (!t) return fail(GSB_ERR_ARG, "gsb_tracker_debug_copy: null", cudaSuccess);
     cudaStream_t st = t->stream;
-    if (flatten_ids && t->last_n_isects > 0)
-        TCK(cudaMemcpyAsync(flatten_ids, t->flatten_ids, sizeof(int) * (size_t)t->last_n_isects, cudaMemcpyDeviceToDevice, st), "debug copy");
-    if (offsets)
-        TCK(cudaMemcpyAsync(offsets, t->offsets, sizeof(int) * ((size_t)t->C * t->n_tiles + 1), cudaMemcpyDeviceToDevice, st), "debug copy");
+    // the loop keeps fixed-capacity bins; gsplat's compact layout (isect_offsets, flatten_ids[M]) is rebuilt here
+    if (flatten_ids || offsets) {
+        const size_t nb = (size_t)t->C * t->n_tiles;
+        std::vector<int2> rg(nb);
+        TCK(cudaMemcpyAsync(rg.data(), t->ranges, sizeof(int2) * nb, cudaMemcpyDeviceToHost, st), "debug copy");
+        TCK(cudaStreamSynchronize(st), "debug copy sync");
+        std::vector<int> off(nb + 1);
+        off[0] = 0;
+        for (size_t b = 0; b < nb; ++b) off[b + 1] = off[b] + (rg[b].y - rg[b].x);
+        TCK(cudaMemcpyAsync(t->offsets, off.data(), sizeof(int) * (nb + 1), cudaMemcpyHostToDevice, st), "debug copy");
+        if (offsets)
+            TCK(cudaMemcpyAsync(offsets, t->offsets, sizeof(int) * (nb + 1), cudaMemcpyDeviceToDevice, st), "debug copy");
+        if (flatten_ids && off[nb] > 0) launch_compact_bins((int)nb, t->ranges, t->flatten_ids, t->offsets, flatten_ids, st);
+        TCK(cudaStreamSynchronize(st), "debug copy sync");   // off is a temporary
+    }
     if (records)
         TCK(cudaMemcpyAsync(records, t->rec, sizeof(float) * 8 * (size_t)t->C * t->N, cudaMemcpyDeviceToDevice, st), "debug copy");
     TCK(cudaStreamSynchronize(st), "debug copy sync");

@@ -265,7 +265,7 @@ def test_one_iteration_with_normal_term_matches_oracle(gsb, mode, dim):
     assert abs(st["loss"] - float(tot)) / float(tot) < 1e-4
     assert U.rel_err(st["g_q"], q.grad.numpy()) < 1e-3, (st["g_q"], q.grad)
     assert U.rel_err(st["g_t"], t.grad.numpy()) < 1e-3, (st["g_t"], t.grad)
-    assert trk.counters()["launches_per_iter"] == (9 if mode == "reference" else 8)
+    assert trk.counters()["launches_per_iter"] == (7 if mode == "reference" else 6)
     trk.close()
 
 
