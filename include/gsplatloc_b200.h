@@ -179,11 +179,14 @@ int gsb_tracker_get_counters(gsb_tracker* t, int64_t* n_isects, int64_t* capacit
                              int64_t* total_launches);
 void* gsb_tracker_stream(gsb_tracker* t);
 /* copies of the tracker's intermediates for parity tests, into caller-allocated DEVICE buffers (any may be NULL):
- * sorted flatten_ids [M], tile offsets [C*T+1], projected records [C*N,8] = {x,y,depth,opacity,a,b,c,radius bits} */
+ * sorted flatten_ids [M], tile offsets [C*T+1], projected records [C*N,8] = {x,y,depth,opacity,a,b,c,radius bits}.
+ * The loop keeps one fixed-capacity bin per (camera, tile); this call compacts them into gsplat's layout
+ * (isect_offsets / flatten_ids of IDX:14360-14377). */
 int gsb_tracker_debug_copy(gsb_tracker* t, int32_t* flatten_ids, int32_t* offsets, float* records);
 /* measurement aid: run n_iters iterations un-graphed with CUDA events between the kernels; stage_ms_host[9] gets
  * the mean device time of {pose_begin, project_bin, tile_scan, bin_emit, tile_sort, raster_fwd, loss, raster_bwd,
- * pose_finish} in ms.  The poses advance exactly as in gsb_tracker_run. */
+ * pose_finish} in ms.  pose_begin is fused into pose_finish, tile_scan and bin_emit into the projection (slot
+ * project_bin): those three slots report the event overhead only.  The poses advance exactly as in gsb_tracker_run. */
 int gsb_tracker_profile(gsb_tracker* t, int n_iters, float* stage_ms_host);
 /* one forward only (render at the current poses; used for the GT re-render of geometry.py:69-135) */
 int gsb_tracker_forward(gsb_tracker* t);
