@@ -201,7 +201,8 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(int n_bins, int* __rest
     }
 }
 
-// Scatter (depth bits << 32 | flat index) into the tile bins. PACKED: tracker records; else SoA (op-level).
+// Scatter (depth bits << 32 | flat index) into compact tile bins (op-level gsb_isect_emit, method 0).  PACKED reads the
+// tracker's records instead of SoA arrays (not instantiated any more: the tracker scatters from project_emit_kernel).
 template <bool PACKED>
 __global__ void __launch_bounds__(256) bin_emit_kernel(int CN, int N, const float4* __restrict__ rec,
                                                        const uint2* __restrict__ bbox,
@@ -524,13 +525,6 @@ void launch_tile_hist(int CN, int N, const float* means2d, const int* radii, int
 void launch_tile_scan(int n_bins, int* counts, int* offsets, int* cursor, int* n_isects, int cap, int* overflow,
                       cudaStream_t st) {
     tile_scan_kernel<<<1, 1024, 0, st>>>(n_bins, counts, offsets, cursor, n_isects, cap, overflow);
-}
-
-void launch_bin_emit_packed(int CN, int N, const float4* rec, const uint2* bbox, int tile_w, int tile_h, int* cursor,
-                            uint64_t* keys, int cap, const int* stop, cudaStream_t st) {
-    if (CN == 0) return;
-    bin_emit_kernel<true><<<(CN + 255) / 256, 256, 0, st>>>(CN, N, rec, bbox, nullptr, nullptr, nullptr, GSB_TILE,
-                                                            tile_w, tile_h, cursor, keys, cap, stop);
 }
 
 void launch_bin_emit_soa(int CN, int N, const float* means2d, const int* radii, const float* depths, int tile_size,

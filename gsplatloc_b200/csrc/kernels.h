@@ -46,8 +46,6 @@ void launch_tile_hist(int CN, int N, const float* means2d, const int* radii, int
                       int* tiles_per_gauss, int* counts, cudaStream_t st);
 void launch_tile_scan(int n_bins, int* counts, int* offsets, int* cursor, int* n_isects, int cap, int* overflow,
                       cudaStream_t st);
-void launch_bin_emit_packed(int CN, int N, const float4* rec, const uint2* bbox, int tile_w, int tile_h, int* cursor,
-                            uint64_t* keys, int cap, const int* stop, cudaStream_t st);
 void launch_bin_emit_soa(int CN, int N, const float* means2d, const int* radii, const float* depths, int tile_size,
                          int tile_w, int tile_h, int* cursor, uint64_t* keys, int cap, cudaStream_t st);
 void launch_tile_sort(int C, int n_tiles, int tile_bits, const int* offsets, uint64_t* keys, int* flatten_ids,

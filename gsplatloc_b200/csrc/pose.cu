@@ -58,12 +58,13 @@ __device__ __forceinline__ void adam_update(float* p, float* m, float* v, const 
     }
 }
 
-__global__ void __launch_bounds__(256) pose_finish_kernel(
+#define POSE_FINISH_THREADS 512   // one block per camera; wide so that the 2T tile partials are a few loads per thread
+__global__ void __launch_bounds__(POSE_FINISH_THREADS) pose_finish_kernel(
     int C, int n_tiles, int n_loss_blocks, const float* __restrict__ partials,
     const float* __restrict__ loss_partials, float* __restrict__ viewmats, gsb_pose_state* __restrict__ state,
     int* __restrict__ stop, gsb_tracker_config cfg, float inv_pixels, float inv_rows3,
     float* __restrict__ history, int history_cap) {
-    __shared__ float red[15][8];
+    __shared__ float red[15][POSE_FINISH_THREADS / 32];
     const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     if (state[c].stopped) return;
     // fixed-order two-level sums: 12 pose-gradient numbers over tiles, 2 loss sums over loss blocks
@@ -73,7 +74,7 @@ __global__ void __launch_bounds__(256) pose_finish_kernel(
     // (independent loads, unrolled so that several L2 round trips are in flight per thread)
     const float* P = partials + (size_t)c * n_tiles * 12;
 #pragma unroll 4
-    for (int i = tid; i < n_tiles; i += 256) {
+    for (int i = tid; i < n_tiles; i += POSE_FINISH_THREADS) {
         const float4* p4 = reinterpret_cast<const float4*>(P + (size_t)i * 12);
         float4 a = p4[0], b = p4[1], d = p4[2];
         acc[0] += a.x; acc[1] += a.y; acc[2] += a.z; acc[3] += a.w;
@@ -82,7 +83,7 @@ __global__ void __launch_bounds__(256) pose_finish_kernel(
     }
     const float* L = loss_partials + (size_t)c * n_loss_blocks * 3;
 #pragma unroll 4
-    for (int i = tid; i < n_loss_blocks; i += 256) {
+    for (int i = tid; i < n_loss_blocks; i += POSE_FINISH_THREADS) {
         acc[12] += L[i * 3];
         acc[13] += L[i * 3 + 1];
         acc[14] += L[i * 3 + 2];
@@ -100,7 +101,7 @@ __global__ void __launch_bounds__(256) pose_finish_kernel(
     for (int k = 0; k < 15; ++k) {
         float v = 0.f;
 #pragma unroll
-        for (int w = 0; w < 8; ++w) v += red[k][w];
+        for (int w = 0; w < POSE_FINISH_THREADS / 32; ++w) v += red[k][w];
         g[k] = v;
     }
     // g[0..8] = d/dR_wc (row-major), g[9..11] = d/dt_wc
@@ -198,7 +199,7 @@ void launch_pose_begin(int C, const gsb_pose_state* state, float* viewmats, cuda
 void launch_pose_finish(int C, int n_tiles, int n_loss_blocks, const float* partials, const float* loss_partials,
                         float* viewmats, gsb_pose_state* state, int* stop, gsb_tracker_config cfg,
                         float inv_pixels, float inv_rows3, float* history, int history_cap, cudaStream_t st) {
-    pose_finish_kernel<<<C, 256, 0, st>>>(C, n_tiles, n_loss_blocks, partials, loss_partials, viewmats, state, stop,
+    pose_finish_kernel<<<C, POSE_FINISH_THREADS, 0, st>>>(C, n_tiles, n_loss_blocks, partials, loss_partials, viewmats, state, stop,
                                           cfg, inv_pixels, inv_rows3, history, history_cap);
 }
 

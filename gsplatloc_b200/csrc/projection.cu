@@ -281,10 +281,19 @@ __global__ void __launch_bounds__(256) project_emit_kernel(
             const uint32_t sbw = __shfl_sync(0xffffffffu, bw, src);
             const int sexcl = __shfl_sync(0xffffffffu, excl, src);
             const uint32_t shi = __shfl_sync(0xffffffffu, key_hi, src), slo = __shfl_sync(0xffffffffu, (uint32_t)i, src);
+            // neighbouring Gaussians with the same big box meet in the same tiles within a round: aggregate again
+            int tile = -1 - lane;
             if (w < total) {
                 const uint32_t t = (uint32_t)(w - sexcl);
-                const int tile = (int)((sy0 + t / sbw) * tile_w + sx0 + t % sbw);
-                const int pos = atomicAdd(cur + tile, 1);
+                tile = (int)((sy0 + t / sbw) * tile_w + sx0 + t % sbw);
+            }
+            const unsigned g2 = __match_any_sync(0xffffffffu, tile);
+            const int ldr = __ffs(g2) - 1;
+            int base = 0;
+            if (w < total && lane == ldr) base = atomicAdd(cur + tile, __popc(g2));
+            base = __shfl_sync(0xffffffffu, base, ldr);
+            if (w < total) {
+                const int pos = base + __popc(g2 & ((1u << lane) - 1u));
                 if (pos < tile_cap) kbase[(size_t)tile * tile_cap + pos] = ((uint64_t)shi << 32) | slo; else over = true;
             }
         }

@@ -34,6 +34,10 @@ struct gsb_tracker {
     float *means = nullptr, *quats = nullptr, *scales = nullptr, *opac = nullptr;
     float *gt = nullptr, *Ks = nullptr, *viewmats = nullptr;
     gsb_pose_state* state = nullptr;
+    gsb_pose_state* state_bak = nullptr;   // poses at the start of the current run (restored when a bin overflows)
+    float* viewmats_bak = nullptr;
+    int* stop_bak = nullptr;
+    int overflow_retries = 0;
     int* stop = nullptr;
     float4* rec = nullptr;
     uint2* bbox = nullptr;
@@ -109,6 +113,25 @@ static void enqueue_iteration(gsb_tracker* t, bool forward_only, cudaEvent_t* ma
 #undef GSB_MARK
 }
 
+// (Re)allocate the fixed-capacity tile bins: keys, sorted ids and patch masks for C * tiles * tile_cap entries.
+static int resize_bins(gsb_tracker* t, int want_cap) {
+    const int64_t want = (int64_t)t->C * t->n_tiles * want_cap;
+    if (want >= ((int64_t)1 << 31))
+        return fail(GSB_ERR_ARG, "tracker: cameras x tiles x bin capacity exceeds 2^31 entries", cudaSuccess);
+    TCK(cudaStreamSynchronize(t->stream), "sync");
+    if (t->keys) cudaFree(t->keys);
+    if (t->flatten_ids) cudaFree(t->flatten_ids);
+    if (t->masks) cudaFree(t->masks);
+    t->keys = nullptr; t->flatten_ids = nullptr; t->masks = nullptr;
+    TCK(cudaMalloc(&t->keys, sizeof(uint64_t) * (size_t)want), "alloc keys");
+    TCK(cudaMalloc(&t->flatten_ids, sizeof(int) * (size_t)want), "alloc flatten_ids");
+    TCK(cudaMalloc(&t->masks, (size_t)want), "alloc masks");
+    t->cap = want;
+    t->tile_cap = want_cap;
+    invalidate_graph(t);
+    return GSB_OK;
+}
+
 // Size the intersection buffers from a counting pass at the current poses (one sync, outside the loop).
 static int ensure_capacity(gsb_tracker* t) {
     cudaStream_t st = t->stream;
@@ -126,23 +149,13 @@ static int ensure_capacity(gsb_tracker* t) {
     t->total_launches += 3;
     int fullest = 0;
     for (size_t b = 0; b < nb; ++b) fullest = std::max(fullest, off[b + 1] - off[b]);
-    // bins are sized for the fullest tile + 25 % + 64 (poses move by centimetres inside a run); a bin that still
-    // overflows raises the flag and the run is repeated with new sizes
-    const int want_cap = ((fullest + fullest / 4 + 64) + 31) & ~31;
+    // bins are sized for the fullest tile + 50 % + 64; a bin that still fills up during a run (the view moves by tiles
+    // between the start pose and the optimum) is caught by the overflow flag: gsb_tracker_run restores the poses,
+    // doubles the bins and repeats
+    const int want_cap = ((fullest + fullest / 2 + 64) + 31) & ~31;
     if (want_cap > t->tile_cap || t->tile_cap == 0) {
-        const int64_t want = (int64_t)nb * want_cap;
-        if (want >= ((int64_t)1 << 31))
-            return fail(GSB_ERR_ARG, "tracker: cameras x tiles x bin capacity exceeds 2^31 entries", cudaSuccess);
-        if (t->keys) cudaFree(t->keys);
-        if (t->flatten_ids) cudaFree(t->flatten_ids);
-        if (t->masks) cudaFree(t->masks);
-        t->keys = nullptr; t->flatten_ids = nullptr; t->masks = nullptr;
-        TCK(cudaMalloc(&t->keys, sizeof(uint64_t) * (size_t)want), "alloc keys");
-        TCK(cudaMalloc(&t->flatten_ids, sizeof(int) * (size_t)want), "alloc flatten_ids");
-        TCK(cudaMalloc(&t->masks, (size_t)want), "alloc masks");
-        t->cap = want;
-        t->tile_cap = want_cap;
-        invalidate_graph(t);
+        int rc = resize_bins(t, want_cap);
+        if (rc) return rc;
     }
     t->cap_dirty = false;
     return GSB_OK;
@@ -203,6 +216,9 @@ int gsb_tracker_create(gsb_tracker** out, int C, int W, int H, void* stream) {
     TCK(cudaMalloc(&t->viewmats, sizeof(float) * 16 * C), "alloc");
     TCK(cudaMalloc(&t->state, sizeof(gsb_pose_state) * C), "alloc");
     TCK(cudaMalloc(&t->stop, sizeof(int) * C), "alloc");
+    TCK(cudaMalloc(&t->state_bak, sizeof(gsb_pose_state) * C), "alloc");
+    TCK(cudaMalloc(&t->viewmats_bak, sizeof(float) * 16 * C), "alloc");
+    TCK(cudaMalloc(&t->stop_bak, sizeof(int) * C), "alloc");
     TCK(cudaMalloc(&t->counts, sizeof(int) * nb), "alloc");
     TCK(cudaMalloc(&t->offsets, sizeof(int) * (nb + 1)), "alloc");
     TCK(cudaMalloc(&t->cursor, sizeof(int) * nb), "alloc");
@@ -239,7 +255,7 @@ void gsb_tracker_destroy(gsb_tracker* t) {
     void* bufs[] = {t->means, t->quats, t->scales, t->opac, t->gt, t->Ks, t->viewmats, t->state, t->stop, t->rec,
                     t->bbox, t->counts, t->offsets, t->cursor, t->ranges, t->n_isects, t->keys, t->flatten_ids, t->masks, t->ed, t->alpha,
                     t->v_depth, t->v_alpha, t->last_ids, t->partials, t->loss_partials, t->normal_rows,
-                    t->history};
+                    t->history, t->state_bak, t->viewmats_bak, t->stop_bak};
     for (void* b : bufs)
         if (b) cudaFree(b);
     if (t->h_flags) cudaFreeHost(t->h_flags);
@@ -342,40 +358,64 @@ int gsb_tracker_run(gsb_tracker* t, int n_iters, int poll_every, int use_graph, 
         int rc = ensure_capacity(t);
         if (rc) return rc;
     }
-    if (use_graph && !t->graph_valid) {
-        int rc = capture_graph(t);
-        if (rc) return rc;
-    }
-    TCK(cudaEventRecord(t->ev0, t->stream), "event");
+    cudaStream_t st = t->stream;
+    // the poses this run starts from: restored if a tile bin overflows and the run has to be repeated with larger bins
+    TCK(cudaMemcpyAsync(t->state_bak, t->state, sizeof(gsb_pose_state) * t->C, cudaMemcpyDeviceToDevice, st), "snapshot");
+    TCK(cudaMemcpyAsync(t->viewmats_bak, t->viewmats, sizeof(float) * 16 * t->C, cudaMemcpyDeviceToDevice, st), "snapshot");
+    TCK(cudaMemcpyAsync(t->stop_bak, t->stop, sizeof(int) * t->C, cudaMemcpyDeviceToDevice, st), "snapshot");
+    TCK(cudaEventRecord(t->ev0, st), "event");
     int done = 0;
-    bool all_stopped = false;
-    for (int it = 0; it < n_iters && !all_stopped; ++it) {
-        if (use_graph) TCK(cudaGraphLaunch(t->exec, t->stream), "graph launch");
-        else enqueue_iteration(t, false);
-        ++done;
-        if (poll_every > 0 && (it + 1) % poll_every == 0 && it + 1 < n_iters) {
-            TCK(cudaMemcpyAsync(t->h_flags, t->stop, sizeof(int) * t->C, cudaMemcpyDeviceToHost, t->stream), "poll");
-            TCK(cudaStreamSynchronize(t->stream), "poll sync");
-            all_stopped = true;
-            for (int c = 0; c < t->C; ++c) all_stopped &= (t->h_flags[c] != 0);
+    for (int attempt = 0;; ++attempt) {
+        if (use_graph && !t->graph_valid) {
+            int rc = capture_graph(t);
+            if (rc) return rc;
         }
+        done = 0;
+        bool all_stopped = false, overflowed = false;
+        for (int it = 0; it < n_iters && !all_stopped && !overflowed; ++it) {
+            if (use_graph) TCK(cudaGraphLaunch(t->exec, st), "graph launch");
+            else enqueue_iteration(t, false);
+            ++done;
+            if (poll_every > 0 && (it + 1) % poll_every == 0 && it + 1 < n_iters) {
+                TCK(cudaMemcpyAsync(t->h_flags, t->stop, sizeof(int) * t->C, cudaMemcpyDeviceToHost, st), "poll");
+                TCK(cudaMemcpyAsync(t->h_flags + t->C + 1, t->overflow, sizeof(int), cudaMemcpyDeviceToHost, st), "poll");
+                TCK(cudaStreamSynchronize(st), "poll sync");
+                all_stopped = true;
+                for (int c = 0; c < t->C; ++c) all_stopped &= (t->h_flags[c] != 0);
+                overflowed = t->h_flags[t->C + 1] != 0;
+            }
+        }
+        TCK(cudaMemcpyAsync(t->h_flags + t->C, t->n_isects, sizeof(int) * 2, cudaMemcpyDeviceToHost, st), "flags");
+        TCK(cudaStreamSynchronize(st), "run sync");
+        TCK(cudaGetLastError(), "run");
+        t->total_launches += (int64_t)done * n_launches_per_iter(t);
+        if (!t->h_flags[t->C + 1]) break;
+        // ---- a tile bin filled up: every iteration since then is invalid.  Restore, double the bins, repeat.
+        TCK(cudaMemsetAsync(t->overflow, 0, sizeof(int), st), "clear overflow");
+        TCK(cudaMemsetAsync(t->cursor, 0, sizeof(int) * (size_t)t->C * t->n_tiles, st), "zero cursors");
+        TCK(cudaMemcpyAsync(t->state, t->state_bak, sizeof(gsb_pose_state) * t->C, cudaMemcpyDeviceToDevice, st), "restore");
+        TCK(cudaMemcpyAsync(t->viewmats, t->viewmats_bak, sizeof(float) * 16 * t->C, cudaMemcpyDeviceToDevice, st), "restore");
+        TCK(cudaMemcpyAsync(t->stop, t->stop_bak, sizeof(int) * t->C, cudaMemcpyDeviceToDevice, st), "restore");
+        if (attempt >= 5 || (int64_t)t->tile_cap * 2 * t->C * t->n_tiles >= ((int64_t)1 << 31)) {
+            t->cap_dirty = true;
+            return fail(GSB_ERR_OVERFLOW, "gsb_tracker_run: a tile bin overflowed and could not be grown further; the poses "
+                                          "were restored to the start of the run", cudaSuccess);
+        }
+        // at least the sizing rule at the restored poses, and at least twice what just proved too small
+        const int failed_cap = t->tile_cap;
+        int rc = ensure_capacity(t);
+        if (rc) return rc;
+        if (t->tile_cap < 2 * failed_cap) {
+            rc = resize_bins(t, 2 * failed_cap);
+            if (rc) return rc;
+        }
+        ++t->overflow_retries;
     }
-    TCK(cudaEventRecord(t->ev1, t->stream), "event");
-    TCK(cudaMemcpyAsync(t->h_flags + t->C, t->n_isects, sizeof(int) * 2, cudaMemcpyDeviceToHost, t->stream), "flags");
-    TCK(cudaStreamSynchronize(t->stream), "run sync");
-    TCK(cudaGetLastError(), "run");
-    t->total_launches += (int64_t)done * n_launches_per_iter(t);
+    TCK(cudaEventRecord(t->ev1, st), "event");
+    TCK(cudaStreamSynchronize(st), "run sync");
     t->last_n_isects = t->h_flags[t->C];
     if (iters_done) *iters_done = done;
     if (elapsed_ms) TCK(cudaEventElapsedTime(elapsed_ms, t->ev0, t->ev1), "elapsed");
-    if (t->h_flags[t->C + 1]) {
-        t->cap_dirty = true;  // regrow on the next run
-        t->cap = 0;
-        t->tile_cap = 0;
-        cudaMemsetAsync(t->overflow, 0, sizeof(int), t->stream);
-        cudaMemsetAsync(t->cursor, 0, sizeof(int) * (size_t)t->C * t->n_tiles, t->stream);
-        return fail(GSB_ERR_OVERFLOW, "gsb_tracker_run: intersection buffer overflowed; poses must be reset and the run repeated", cudaSuccess);
-    }
     return GSB_OK;
 }
 
@@ -459,6 +499,20 @@ int gsb_tracker_get_counters(gsb_tracker* t, int64_t* n_isects, int64_t* capacit
     if (capacity) *capacity = t->cap;
     if (launches_per_iter) *launches_per_iter = n_launches_per_iter(t);
     if (total_launches) *total_launches = t->total_launches;
+    return GSB_OK;
+}
+
+int gsb_tracker_debug_limit_bins(gsb_tracker* t, int tile_cap) {
+    if (!t || tile_cap <= 0) return fail(GSB_ERR_ARG, "gsb_tracker_debug_limit_bins: bad arguments", cudaSuccess);
+    if (!t->have_map || !t->have_obs || !t->have_pose)
+        return fail(GSB_ERR_ARG, "gsb_tracker_debug_limit_bins: map, observation and poses must be set first", cudaSuccess);
+    if (t->cap_dirty) {
+        int rc = ensure_capacity(t);
+        if (rc) return rc;
+    }
+    t->tile_cap = std::min(t->tile_cap, tile_cap);   // the buffers stay as large as they are
+    t->cap = (int64_t)t->C * t->n_tiles * t->tile_cap;
+    invalidate_graph(t);                              // the capacity is a kernel argument
     return GSB_OK;
 }
 

@@ -205,6 +205,10 @@ class PoseTracker:
         return {"n_isects": m.value, "capacity": cap.value, "launches_per_iter": lpi.value,
                 "total_launches": tot.value}
 
+    def debug_limit_bins(self, tile_cap: int):
+        """Test aid: cap the per-tile bins so that the next ``run`` overflows (``RuntimeError``, code 3)."""
+        _lib.check(self._L.gsb_tracker_debug_limit_bins(self._h, int(tile_cap)), "tracker_debug_limit_bins")
+
     def debug_tensors(self):
         """Sorted flatten_ids [M], tile offsets [C*T+1] and projected records [C*N,8] of the last forward
         (copies), for parity tests."""

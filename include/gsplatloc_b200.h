@@ -183,6 +183,10 @@ void* gsb_tracker_stream(gsb_tracker* t);
  * The loop keeps one fixed-capacity bin per (camera, tile); this call compacts them into gsplat's layout
  * (isect_offsets / flatten_ids of IDX:14360-14377). */
 int gsb_tracker_debug_copy(gsb_tracker* t, int32_t* flatten_ids, int32_t* offsets, float* records);
+/* test aid for the overflow path: shrink the per-tile bin capacity below what the sizing pass chose, so that the next
+ * gsb_tracker_run fills a bin, raises the flag and returns GSB_ERR_OVERFLOW (the bins are re-sized by the next
+ * gsb_tracker_set_poses + run). */
+int gsb_tracker_debug_limit_bins(gsb_tracker* t, int tile_cap);
 /* measurement aid: run n_iters iterations un-graphed with CUDA events between the kernels; stage_ms_host[9] gets
  * the mean device time of {pose_begin, project_bin, tile_scan, bin_emit, tile_sort, raster_fwd, loss, raster_bwd,
  * pose_finish} in ms.  pose_begin is fused into pose_finish, tile_scan and bin_emit into the projection (slot

@@ -341,3 +341,26 @@ def test_one_iteration_anisotropic_map_matches_oracle(gsb):
     assert U.rel_err(st["g_q"], q.grad.numpy()) < 1e-3, (st["g_q"], q.grad)
     assert U.rel_err(st["g_t"], t.grad.numpy()) < 1e-3, (st["g_t"], t.grad)
     trk.close()
+
+
+def test_bin_overflow_is_caught_and_the_run_repeated(gsb):
+    """A tile bin that fills up must not corrupt anything silently: gsb_tracker_run notices the flag, restores the poses
+    of the start of the run, doubles the bins and repeats -- the result is exactly that of an undisturbed tracker."""
+    fp = U.frame(U.SMALL_CAM, stride=2, seed=42)
+    c2w0 = _start_pose(fp)
+    ref = _tracker(gsb, fp, c2w0, fp.src_depth, early_stop=False)
+    ref.run(30, poll_every=0)
+    want = ref.states()[0]
+    ref.close()
+    for poll in (0, 10):                      # flag seen at the end of the run / at a poll point
+        trk = _tracker(gsb, fp, c2w0, fp.src_depth, early_stop=False)
+        trk.debug_limit_bins(8)
+        cap0 = trk.counters()["capacity"]
+        trk.run(30, poll_every=poll)
+        got = trk.states()[0]
+        assert trk.counters()["capacity"] > cap0
+        assert got["iter"] == want["iter"] == 30
+        assert np.array_equal(np.asarray(got["q"]), np.asarray(want["q"]))
+        assert np.array_equal(np.asarray(got["t"]), np.asarray(want["t"]))
+        assert got["loss"] == want["loss"]
+        trk.close()
