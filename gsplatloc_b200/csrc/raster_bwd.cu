@@ -107,7 +107,18 @@ __device__ __noinline__ void lift_to_pose(const LiftCtx* __restrict__ ctx, int f
         p.pz = camera.R[6] * mean[0] + camera.R[7] * mean[1] + camera.R[8] * mean[2] + camera.t[2];
         persp_project(camera, S, ctx->W, ctx->H, ctx->eps2d, -1.f, p);
         project_vjp(camera, p, S, g0, g1, g2, g3, g4, g5, v_pc, vS);
-        pose_accumulate(camera, mean, S, v_pc, vS, acc, acc + 9);
+        // v_R = v_pc mean^T (+ 2 vSc R S, dropped): with S = s^2 I the covariance term is 2 s^2 vSc R, i.e. R times a
+        // SYMMETRIC matrix seen from the right (R^T (vSc R) is symmetric) -- orthogonal to every direction R K (K skew)
+        // in which a rotation can move, so it contributes nothing to d loss / d quaternion (pose_finish contracts v_R
+        // with dR/dq, which is tangent to SO(3)), and the translation gradient never sees v_R's symmetric part either:
+        // the camera-space covariance s^2 I simply does not depend on the pose.  (g_viewmat in the pose state is
+        // therefore the tangent-relevant part only on isotropic maps.)
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+#pragma unroll
+            for (int j = 0; j < 3; ++j) acc[i * 3 + j] = v_pc[i] * mean[j];
+            acc[9 + i] = v_pc[i];
+        }
     } else {
         const float4 q4 = __ldg(reinterpret_cast<const float4*>(ctx->quats) + n);
         const float q[4] = {q4.x, q4.y, q4.z, q4.w};
