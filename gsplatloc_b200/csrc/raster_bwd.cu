@@ -83,12 +83,13 @@ struct LiftCtx {
 };
 
 // A.6 for one Gaussian: the six patch-summed numbers (v_xy, v_conic, v_depth) -> 12 pose-gradient numbers, accumulated
-// into this thread's column pose_col[k * col_stride].  Out of line on purpose: the camera, the re-projection
-// temporaries and the accumulators must not compete for registers with the replay loop.
+// into this thread's column pose_col[k * col_stride] in shared memory (twelve more live registers would not fit the
+// replay loop's 128).  Inlined: with the lean isotropic path it fits without spills, and an out-of-line call cost 4 us
+// of register save / restore per launch.
 // Isotropic maps (GsplatLoc's: scales = one KNN distance repeated three times, geometry.py:44-66) take a short cut:
 // Sigma = Rq diag(s,s,s)^2 Rq^T = s^2 I for ANY quaternion and Sigma_cam = R Sigma R^T = s^2 I, so the quaternion
 // and the two 3x3 congruences drop out (the literal zeros below fold away after inlining).
-__device__ __noinline__ void lift_to_pose(const LiftCtx* __restrict__ ctx, int flat_id, float g0, float g1, float g2,
+__device__ __forceinline__ void lift_to_pose(const LiftCtx* __restrict__ ctx, int flat_id, float g0, float g1, float g2,
                                           float g3, float g4, float g5, float* __restrict__ pose_col,
                                           int col_stride) {
     const Cam camera = ctx->cam;
