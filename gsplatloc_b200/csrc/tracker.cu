@@ -444,6 +444,12 @@ int gsb_tracker_profile(gsb_tracker* t, int n_iters, float* stage_ms_host) {
     TCK(cudaMemcpyAsync(t->h_flags + t->C, t->n_isects, sizeof(int) * 2, cudaMemcpyDeviceToHost, t->stream), "flags");
     TCK(cudaStreamSynchronize(t->stream), "profile sync");
     t->last_n_isects = t->h_flags[t->C];
+    if (t->h_flags[t->C + 1]) {   // no restore / repeat here: the timings would be of invalid iterations
+        cudaMemsetAsync(t->overflow, 0, sizeof(int), t->stream);
+        cudaMemsetAsync(t->cursor, 0, sizeof(int) * (size_t)t->C * t->n_tiles, t->stream);
+        t->cap_dirty = true;
+        return fail(GSB_ERR_OVERFLOW, "gsb_tracker_profile: a tile bin overflowed; set the poses again and repeat", cudaSuccess);
+    }
     return GSB_OK;
 }
 
@@ -461,6 +467,12 @@ int gsb_tracker_forward(gsb_tracker* t) {
     TCK(cudaGetLastError(), "forward");
     t->total_launches += 3;
     t->last_n_isects = t->h_flags[t->C];
+    if (t->h_flags[t->C + 1]) {   // cannot happen after a sizing pass at these very poses; checked all the same
+        cudaMemsetAsync(t->overflow, 0, sizeof(int), t->stream);
+        cudaMemsetAsync(t->cursor, 0, sizeof(int) * (size_t)t->C * t->n_tiles, t->stream);
+        t->cap_dirty = true;
+        return fail(GSB_ERR_OVERFLOW, "gsb_tracker_forward: a tile bin overflowed", cudaSuccess);
+    }
     return GSB_OK;
 }
 
