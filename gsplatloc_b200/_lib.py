@@ -80,6 +80,7 @@ _SIGS = {
     "gsb_init_gs_scales": (c_i, [c_i, c_p, c_i, c_f, c_i, c_p, c_p]),
     "gsb_depth_to_points": (c_i, [c_i, c_i, c_p, C.POINTER(c_f), C.POINTER(c_f), c_p, c_p]),
     "gsb_transform_points": (c_i, [c_i, c_p, C.POINTER(c_f), c_p, c_p]),
+    "gsb_points_median_cov": (c_i, [c_i, c_p, C.POINTER(c_f), C.POINTER(c_f), c_p]),
 }
 
 EXPORTS = tuple(_SIGS)

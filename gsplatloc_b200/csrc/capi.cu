@@ -278,4 +278,13 @@ int gsb_transform_points(int N, const float* points_in, const float* T_host, flo
     return GSB_OK;
 }
 
+int gsb_points_median_cov(int N, const float* points, float* median_host, float* cov_host, void* stream) {
+    if (N <= 0 || !points || !median_host || !cov_host)
+        return fail(GSB_ERR_ARG, "gsb_points_median_cov: need N > 0 and non-null pointers", cudaSuccess);
+    const char* what = "";
+    cudaError_t e = points_median_cov(N, points, median_host, cov_host, (cudaStream_t)stream, &what);
+    if (e != cudaSuccess) return fail(GSB_ERR_CUDA, what, e);
+    return GSB_OK;
+}
+
 }  // extern "C"

@@ -104,6 +104,8 @@ cudaError_t knn_run(int N, const float* pts, int k, float* sq_dists, float* scal
                     int* grid_dims_out, cudaStream_t st, const char** what);
 void launch_depth_to_points(int W, int H, const float* depth, const float* K9_host, const float* T16_host,
                             float* points, cudaStream_t st);
+cudaError_t points_median_cov(int N, const float* pts, float* median_host, float* cov_host, cudaStream_t st,
+                              const char** what);
 void launch_transform_points(int N, const float* in, const float* T16_host, float* out, cudaStream_t st);
 
 }  // namespace gsb

@@ -92,3 +92,53 @@ def compute_depth_gt(points: Tensor, rgbs: Tensor | None, Ks: Tensor, c2w: Tenso
                                   width=width, height=height, far_plane=1e10, near_plane=1e-2, render_mode="ED",
                                   rasterize_mode="classic")
     return renders.squeeze(0).squeeze(-1)
+
+
+# ---------------------------------------------------------------------------------------------- PCA normalisation
+@torch.no_grad()
+def align_principle_axes(point_cloud: Tensor) -> Tensor:
+    """src/data/normalize.py:7-50: SE(3) matrix that moves the cloud's per-axis median to the origin and its principal
+    axes (eigenvectors of the covariance, largest eigenvalue first, right-handed) onto x, y, z.  The two reductions
+    over the N points (median, covariance) run on the GPU (``gsb_points_median_cov``); the 3x3 ``eigh``, the
+    determinant flip and the assembly are host code, as cheap as they are in the reference."""
+    pts = _chk(point_cloud.detach(), "point_cloud")
+    assert pts.dim() == 2 and pts.shape[1] == 3, pts.shape
+    med = (C.c_float * 3)()
+    cov = (C.c_float * 9)()
+    _lib.check(_lib.lib().gsb_points_median_cov(pts.shape[0], _p(pts), med, cov, _stream()), "points_median_cov")
+    centroid = torch.tensor(list(med), dtype=torch.float32)
+    covariance = torch.tensor(list(cov), dtype=torch.float32).reshape(3, 3)
+    eigenvalues, eigenvectors = torch.linalg.eigh(covariance)
+    eigenvectors = eigenvectors[:, eigenvalues.argsort(descending=True)]
+    if torch.det(eigenvectors) < 0:
+        eigenvectors[:, 0] *= -1
+    rotation = eigenvectors.t()
+    transform = torch.eye(4)
+    transform[:3, :3] = rotation
+    transform[:3, 3] = -torch.mv(rotation, centroid)
+    return transform.to(pts.device)
+
+
+@torch.no_grad()
+def transform_cameras(matrix: Tensor, c2w: Tensor):
+    """src/data/normalize.py:75-101: ``matrix @ c2w[n]`` with the rotation block re-normalised by the norm of its first
+    row; returns (transformed [N,4,4], scaling [N,1]).  A handful of 4x4 products: plain torch."""
+    assert tuple(matrix.shape) == (4, 4)
+    assert c2w.dim() == 3 and tuple(c2w.shape[1:]) == (4, 4)
+    transformed = torch.einsum("ki,nij->nkj", matrix, c2w)
+    scaling = torch.norm(transformed[:, 0, :3], p=2, dim=1, keepdim=True)
+    transformed[:, :3, :3] /= scaling.unsqueeze(-1)
+    return transformed, scaling
+
+
+@torch.no_grad()
+def normalize_2C(tar_points: Tensor, tar_pose: Tensor, src_points: Tensor, src_pose: Tensor):
+    """src/data/normalize.py:104-124 on plain tensors instead of ``RGBDImage`` objects: the transform is computed from the
+    TARGET cloud and applied to both clouds and both poses.  Returns (tar_points, tar_pose, src_points, src_pose,
+    scale_factor) with scale_factor the target's, as the reference returns it."""
+    T = align_principle_axes(tar_points)
+    out_t = transform_points(T, tar_points)
+    pose_t, scale = transform_cameras(T.to(tar_pose.device), tar_pose.unsqueeze(0))
+    out_s = transform_points(T, src_points)
+    pose_s, _ = transform_cameras(T.to(src_pose.device), src_pose.unsqueeze(0))
+    return out_t, pose_t.squeeze(0), out_s, pose_s.squeeze(0), scale

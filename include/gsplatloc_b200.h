@@ -215,6 +215,11 @@ int gsb_depth_to_points(int width, int height, const float* depth, const float* 
 /* transform_points (geometry.py:23-41): out[N,3] = in @ R^T + t, T_host row-major 4x4. in == out allowed. */
 int gsb_transform_points(int N, const float* points_in, const float* T_host, float* points_out, void* stream);
 
+/* the reductions of align_principle_axes (src/data/normalize.py:7-50): median_host[3] = torch.median(points, dim=0)
+ * (the lower median), cov_host[9] = torch.cov((points - median).t()) (unbiased, row-major).  The 3x3 eigh, the
+ * determinant flip and the SE(3) assembly are host code (gsplatloc_b200/geometry.py).  Synchronises the stream. */
+int gsb_points_median_cov(int N, const float* points, float* median_host, float* cov_host, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -73,3 +73,29 @@ def compute_depth_gt(points: np.ndarray, Ks: np.ndarray, c2w: np.ndarray, height
                                 sh_degree=1, viewmats=torch.linalg.inv(c2w_t), Ks=Ks_t, width=width, height=height,
                                 far_plane=1e10, near_plane=1e-2, render_mode="ED", rasterize_mode="classic")
     return r.squeeze(0).squeeze(-1).numpy()
+
+
+def align_principle_axes(points: np.ndarray) -> np.ndarray:
+    """src/data/normalize.py:7-50 in torch on the CPU (float32 like the reference): lower median per axis, unbiased
+    covariance, eigh, eigenvectors by descending eigenvalue, determinant flip, [R | -R c]."""
+    import torch
+    pc = torch.tensor(np.asarray(points, dtype=np.float32))
+    centroid = torch.median(pc, dim=0).values
+    cov = torch.cov((pc - centroid).t())
+    w, v = torch.linalg.eigh(cov)
+    v = v[:, w.argsort(descending=True)]
+    if torch.det(v) < 0:
+        v[:, 0] *= -1
+    R = v.t()
+    T = torch.eye(4)
+    T[:3, :3] = R
+    T[:3, 3] = -torch.mv(R, centroid)
+    return T.numpy()
+
+
+def median_cov(points: np.ndarray):
+    """The two reductions of align_principle_axes in float64 (numpy): lower median per axis, unbiased covariance."""
+    p = np.asarray(points, dtype=np.float64)
+    med = np.sort(p, axis=0)[(p.shape[0] - 1) // 2]
+    d = p - med
+    return med, np.cov(d.T, ddof=1)

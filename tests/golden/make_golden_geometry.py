@@ -65,6 +65,14 @@ def main():
     gt = geo.compute_depth_gt(torch.tensor(src), torch.zeros(src.shape[0], 3), torch.tensor(out["K"])[None],
                               torch.tensor(out["gt_c2w"])[None], fp.H, fp.W)
     out["gt_depth"] = gt.detach().numpy().astype(np.float32)
+    # PCA normalisation (src/data/normalize.py): the reference's own align_principle_axes / transform_cameras
+    import importlib
+    nz = importlib.import_module("src.data.normalize")
+    for tag, pts in (("lattice", lattice), ("blob", blob)):
+        out[tag + "_pca_T"] = nz.align_principle_axes(torch.tensor(pts)).numpy()
+    poses = torch.tensor(np.stack([fp.tar_c2w, fp.src_c2w]).astype(np.float32))
+    tc, sc = nz.transform_cameras(torch.tensor(out["lattice_pca_T"]), poses.clone())
+    out["pca_poses_in"] = poses.numpy(); out["pca_poses_out"] = tc.numpy(); out["pca_scaling"] = sc.numpy()
     out["cam"] = np.array([fp.W, fp.H], dtype=np.int64)
     path = os.path.join(HERE, "ref_geometry_small.npz")
     np.savez_compressed(path, **out)

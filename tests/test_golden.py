@@ -134,3 +134,17 @@ def test_geometry_oracle_depth_gt_matches_reference_code(gold_geo):
     d = geo.compute_depth_gt(gold_geo["gt_points"], gold_geo["K"], gold_geo["gt_c2w"], H, W)
     assert d.shape == (H, W)
     assert U.rel_err(d, gold_geo["gt_depth"]) < 1e-5
+
+
+@pytest.mark.parametrize("tag", ["lattice", "blob"])
+def test_geometry_oracle_pca_matches_reference_code(gold_geo, tag):
+    """align_principle_axes / transform_cameras (src/data/normalize.py) run by the fixture generator vs the oracle."""
+    from oracle import geometry_oracle as geo
+    T = geo.align_principle_axes(gold_geo[tag + "_points"])
+    assert np.allclose(T, gold_geo[tag + "_pca_T"], atol=1e-6)
+    med, cov = geo.median_cov(gold_geo[tag + "_points"])
+    R = gold_geo[tag + "_pca_T"][:3, :3]
+    assert np.allclose(-R @ med, gold_geo[tag + "_pca_T"][:3, 3], atol=1e-5)
+    D = R @ cov @ R.T                                   # the reference's axes diagonalise the float64 covariance
+    assert np.abs(D - np.diag(np.diag(D))).max() < 1e-5 * np.abs(D).max()
+    assert D[0, 0] >= D[1, 1] >= D[2, 2] and np.linalg.det(R) > 0

@@ -142,3 +142,39 @@ def test_per_frame_setup_on_the_gpu_reproduces_the_host_pipeline(geo):
     ref = geo_o.compute_depth_gt(cam_pts.cpu().numpy(), K, np.eye(4), H, W, reference_faithful=False)
     err = np.abs(d - ref) / np.maximum(np.abs(ref), 1e-6)
     assert np.mean(err > 1e-4) < 1e-3, float(np.mean(err > 1e-4))
+
+
+@pytest.mark.parametrize("tag", ["lattice", "blob"])
+def test_pca_normalisation_matches_the_reference_fixture(geo, gold, tag):
+    """Row f2 (rest): align_principle_axes with the median / covariance reductions on the GPU, transform_cameras and
+    normalize_2C, against the reference's own normalize.py (fixture) and the float64 reductions of the oracle."""
+    from gsplatloc_b200 import _lib
+    import ctypes as C
+    pts = torch.tensor(gold[tag + "_points"]).cuda()
+    med, cov = (C.c_float * 3)(), (C.c_float * 9)()
+    _lib.check(_lib.lib().gsb_points_median_cov(pts.shape[0], pts.data_ptr(), med, cov,
+                                                torch.cuda.current_stream().cuda_stream), "points_median_cov")
+    med_o, cov_o = geo_o.median_cov(gold[tag + "_points"])
+    assert np.array_equal(np.array(list(med), dtype=np.float32), med_o.astype(np.float32))     # a selection: exact
+    assert np.allclose(np.array(list(cov)).reshape(3, 3), cov_o, rtol=1e-5, atol=1e-7)
+    T = geo.align_principle_axes(pts).cpu().numpy()
+    assert np.allclose(T, gold[tag + "_pca_T"], atol=2e-5), np.abs(T - gold[tag + "_pca_T"]).max()
+
+
+def test_transform_cameras_and_normalize_2c(geo, gold):
+    T = torch.tensor(gold["lattice_pca_T"])
+    out, sc = geo.transform_cameras(T, torch.tensor(gold["pca_poses_in"]))
+    assert np.allclose(out.numpy(), gold["pca_poses_out"], atol=1e-6) and np.allclose(sc.numpy(), gold["pca_scaling"], atol=1e-6)
+    tar = torch.tensor(gold["lattice_points"]).cuda()
+    src = torch.tensor(gold["gt_points"]).cuda()
+    tp, tpose, sp, spose, scale = geo.normalize_2C(tar, torch.tensor(gold["pca_poses_in"][0]), src,
+                                                   torch.tensor(gold["pca_poses_in"][1]))
+    assert U.rel_err(tp.cpu().numpy(), geo_o.transform_points(gold["lattice_pca_T"], gold["lattice_points"])) < 1e-4
+    assert U.rel_err(sp.cpu().numpy(), geo_o.transform_points(gold["lattice_pca_T"], gold["gt_points"])) < 1e-4
+    assert np.allclose(tpose.numpy(), gold["pca_poses_out"][0], atol=1e-4) and np.allclose(spose.numpy(), gold["pca_poses_out"][1], atol=1e-4)
+    # after normalisation the target cloud's covariance is diagonal, descending (the per-axis median does not commute
+    # with the rotation, so it is not at the origin in general)
+    _, cov = geo_o.median_cov(tp.cpu().numpy())
+    assert np.abs(cov - np.diag(np.diag(cov))).max() < 1e-4 * np.abs(cov).max()
+    assert cov[0, 0] >= cov[1, 1] >= cov[2, 2]
+    assert abs(float(scale) - 1.0) < 1e-5
