@@ -41,10 +41,16 @@ def main():
     ap.add_argument("--seed", type=int, default=42)
     ap.add_argument("--obs", default="rendered", choices=["rendered", "raw"],
                     help="observation: compute_depth_gt re-render of the source frame (dataset.py:362-372) or raw depth")
+    ap.add_argument("--chain", default="off", choices=["off", "last", "cv"],
+                    help="off: every loop starts at the previous frame's GROUND-TRUTH pose, as the shipped trainer does "
+                         "(gs_trainer_total.py:49-63), frames round-robin over ranks.  last / cv: odometry -- the map is "
+                         "placed at the TRACKED pose of the previous loop and the loop starts there (last) or at the "
+                         "constant-velocity prediction (cv: model.py:41-77); each rank chains a contiguous block")
     args = ap.parse_args()
 
     import torch.distributed as dist
-    from gsplatloc_b200 import PoseTracker, TrackerConfig, geometry as geo, sharding, synthetic as syn
+    from gsplatloc_b200 import PoseTracker, TrackerConfig, geometry as geo, motion, sharding, synthetic as syn
+    from gsplatloc_b200.tracker import quat_t_to_c2w
 
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -56,7 +62,9 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     cam = getattr(syn, args.camera)
-    mine = sharding.frames_of_rank(args.frames, rank, world)
+    chained = args.chain != "off"
+    mine = (list(sharding.hypotheses_of_rank(args.frames, rank, world)) if chained
+            else sharding.frames_of_rank(args.frames, rank, world))
     # ---- the "dataset": every rank ray casts the whole walk (cheap, deterministic) and keeps its own frames
     rng = np.random.default_rng(args.seed)
     scene = syn.make_scene(rng)
@@ -79,9 +87,9 @@ def main():
     trk = PoseTracker(W, H, 1, cfg, device=dev)
     s = args.stride
 
-    def setup(fr):
+    def setup(fr, c2w_map):
         """depth image of the target frame -> map of the pose loop (geometry.py:138-161,23-41,44-66; model.py:136-178)."""
-        pts = geo.depth_to_points(fr["depth_tar"].to(dev, non_blocking=True), Kt, c2w=torch.tensor(fr["c2w_tar"]))
+        pts = geo.depth_to_points(fr["depth_tar"].to(dev, non_blocking=True), Kt, c2w=torch.tensor(c2w_map))
         pts = pts.view(H, W, 3)[s // 2::s, s // 2::s].reshape(-1, 3).contiguous()
         scales = geo.init_gs_scales(pts, 5, reference_faithful=False)
         n = pts.shape[0]
@@ -102,12 +110,13 @@ def main():
         cam_pts = geo.depth_to_points(d, Kt).view(H, W, 3)[s // 2::s, s // 2::s].reshape(-1, 3).contiguous()
         return geo.compute_depth_gt(cam_pts, None, Ks_dev, eye, H, W, reference_faithful=False).contiguous()
 
-    def track(fr):
+    def track(fr, c2w_map=None, c2w_init=None):
         t0 = time.perf_counter()
-        m = setup(fr)
+        c2w_map = fr["c2w_tar"] if c2w_map is None else c2w_map
+        m = setup(fr, c2w_map)
         trk.set_map(*m)
         trk.set_observation(observation(fr), K32)
-        trk.set_poses(fr["c2w_tar"], fr["c2w_src"])
+        trk.set_poses(c2w_map if c2w_init is None else c2w_init, fr["c2w_src"])
         torch.cuda.synchronize(dev)
         t1 = time.perf_counter()
         r = trk.run(None, poll_every=25, use_graph=True)
@@ -121,8 +130,19 @@ def main():
     torch.cuda.synchronize(dev)
     w0 = time.perf_counter()
     rows, iters, t_setup, t_loop = [], 0, 0.0, 0.0
+    est = cv = None
     for f in mine:
-        st, r, ts, tl = track(frames[f])
+        if chained:
+            if est is None:                            # a block starts at its first frame's ground-truth pose
+                est = frames[f]["c2w_tar"]
+                cv = motion.ConstantVelocity(est)
+            st, r, ts, tl = track(frames[f], est, cv.c2w() if args.chain == "cv" else est)
+            est = quat_t_to_c2w(st["q"], st["t"]).astype(np.float32)
+            cv.update_pose(est)                        # the loop's result becomes the current pose ...
+            if args.chain == "cv":
+                cv.update_pose()                       # ... and the next loop starts at the prediction
+        else:
+            st, r, ts, tl = track(frames[f])
         rows.append(sharding.state_to_record(f, rank, st))
         iters += r["iters"]; t_setup += ts; t_loop += tl
     torch.cuda.synchronize(dev)
@@ -138,7 +158,7 @@ def main():
         best = sharding.trajectory_errors(records, use_best=True)
         print(json.dumps({
             "workload": f"{args.camera} {W}x{H}, stride {s} lattice ({(H // s) * (W // s)} Gaussians), {args.frames} frames, "
-                        f"early stop (patience {args.patience}, max {args.max_steps}), observation {args.obs}",
+                        f"early stop (patience {args.patience}, max {args.max_steps}), observation {args.obs}, chain {args.chain}",
             "n_gpus": world, "frames_per_s": round(args.frames / wall, 2), "iters_per_s": round(iters / wall, 1),
             "iters_per_frame": round(iters / max(args.frames, 1), 1), "wall_s": round(wall, 3),
             "setup_share": round(t_setup / max(t_setup + t_loop, 1e-9), 4),
