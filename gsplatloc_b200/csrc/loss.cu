@@ -13,7 +13,10 @@
 namespace gsb {
 
 #define LBX 32
-#define LBY 8
+#ifndef GSB_LOSS_ROWS
+#define GSB_LOSS_ROWS 8
+#endif
+#define LBY GSB_LOSS_ROWS
 #define LW (LBX + 4)
 #define LH (LBY + 4)
 
@@ -106,7 +109,7 @@ __global__ void __launch_bounds__(LBX* LBY) loss_kernel(
     __shared__ float sA[LH][LW], sB[LH][LW];
     __shared__ float sKx[LBY + 2][LBX + 2], sKy[LBY + 2][LBX + 2];
     __shared__ float sHn[NMODE ? 6 : 1][LBY + 2][LBX + 2];   // Hx = dy x G, Hy = G x dx of the halo-1 window
-    __shared__ float s_red[3][8];
+    __shared__ float s_red[3][(LBX * LBY) / 32];
     const int cam = blockIdx.z;
     if (stop && stop[cam]) return;
     const int tid = threadIdx.y * LBX + threadIdx.x;
