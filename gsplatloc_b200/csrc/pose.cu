@@ -5,8 +5,12 @@
 //                d/d(quat), d/d(t) through kornia's R(q/|q|); losses; early-stop bookkeeping; two Adam steps with
 //                coupled weight decay; ExponentialLR.                      gs_trainer_total.py:145-267
 // No host round trip: the reference syncs 2-4 times per step on .item(); here the host only polls a flag.
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 #include "kernels.h"
+
+namespace cg = cooperative_groups;
 
 namespace gsb {
 
@@ -58,23 +62,34 @@ __device__ __forceinline__ void adam_update(float* p, float* m, float* v, const 
     }
 }
 
-#define POSE_FINISH_THREADS 512   // one block per camera; wide so that the 2T tile partials are a few loads per thread
-__global__ void __launch_bounds__(POSE_FINISH_THREADS) pose_finish_kernel(
+// One thread-block CLUSTER per camera: the 2T tile partials (12 floats each) and the loss-block partials are spread
+// over the cluster's blocks, each block reduces its slice in a fixed order, hands 15 sums to the leader's shared memory
+// through distributed shared memory, and the leader's thread 0 does the (scalar) pose arithmetic.  Same result on every
+// run: slice boundaries and summation order are functions of the launch geometry only.
+#ifndef GSB_POSE_CLUSTER
+#define GSB_POSE_CLUSTER 8
+#endif
+#define POSE_FINISH_THREADS 256
+__global__ void __cluster_dims__(GSB_POSE_CLUSTER, 1, 1) __launch_bounds__(POSE_FINISH_THREADS) pose_finish_kernel(
     int C, int n_tiles, int n_loss_blocks, const float* __restrict__ partials,
     const float* __restrict__ loss_partials, float* __restrict__ viewmats, gsb_pose_state* __restrict__ state,
     int* __restrict__ stop, gsb_tracker_config cfg, float inv_pixels, float inv_rows3,
     float* __restrict__ history, int history_cap) {
     __shared__ float red[15][POSE_FINISH_THREADS / 32];
-    const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    if (state[c].stopped) return;
-    // fixed-order two-level sums: 12 pose-gradient numbers over tiles, 2 loss sums over loss blocks
+    __shared__ float cred[GSB_POSE_CLUSTER][16];   // written by every block of the cluster into the LEADER's copy
+    cg::cluster_group cluster = cg::this_cluster();
+    const int rank = (int)cluster.block_rank();
+    const int c = blockIdx.x / GSB_POSE_CLUSTER, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (state[c].stopped) return;                  // the same answer in every block of the cluster
+    // fixed-order sums: 12 pose-gradient numbers over tiles, 3 loss sums over loss blocks
     float acc[15];
 #pragma unroll
     for (int k = 0; k < 15; ++k) acc[k] = 0.f;
+    constexpr int STRIDE = GSB_POSE_CLUSTER * POSE_FINISH_THREADS;
     // (independent loads, unrolled so that several L2 round trips are in flight per thread)
     const float* P = partials + (size_t)c * n_tiles * 12;
-#pragma unroll 4
-    for (int i = tid; i < n_tiles; i += POSE_FINISH_THREADS) {
+#pragma unroll 2
+    for (int i = rank * POSE_FINISH_THREADS + tid; i < n_tiles; i += STRIDE) {
         const float4* p4 = reinterpret_cast<const float4*>(P + (size_t)i * 12);
         float4 a = p4[0], b = p4[1], d = p4[2];
         acc[0] += a.x; acc[1] += a.y; acc[2] += a.z; acc[3] += a.w;
@@ -82,8 +97,8 @@ __global__ void __launch_bounds__(POSE_FINISH_THREADS) pose_finish_kernel(
         acc[8] += d.x; acc[9] += d.y; acc[10] += d.z; acc[11] += d.w;
     }
     const float* L = loss_partials + (size_t)c * n_loss_blocks * 3;
-#pragma unroll 4
-    for (int i = tid; i < n_loss_blocks; i += POSE_FINISH_THREADS) {
+#pragma unroll 2
+    for (int i = rank * POSE_FINISH_THREADS + tid; i < n_loss_blocks; i += STRIDE) {
         acc[12] += L[i * 3];
         acc[13] += L[i * 3 + 1];
         acc[14] += L[i * 3 + 2];
@@ -94,14 +109,22 @@ __global__ void __launch_bounds__(POSE_FINISH_THREADS) pose_finish_kernel(
         if (lane == 0) red[k][wid] = v;
     }
     __syncthreads();
-    if (tid != 0) return;
+    if (tid < 15) {
+        float v = 0.f;
+#pragma unroll
+        for (int w = 0; w < POSE_FINISH_THREADS / 32; ++w) v += red[tid][w];
+        float* leader = cluster.map_shared_rank(&cred[0][0], 0);
+        leader[rank * 16 + tid] = v;
+    }
+    cluster.sync();                                // release / acquire: the leader sees every block's 15 sums
+    if (rank != 0 || tid != 0) return;
     gsb_pose_state s = state[c];   // one bulk read; every update below works on the copy, one bulk write at the end
     float g[15];
 #pragma unroll
     for (int k = 0; k < 15; ++k) {
         float v = 0.f;
 #pragma unroll
-        for (int w = 0; w < POSE_FINISH_THREADS / 32; ++w) v += red[k][w];
+        for (int r = 0; r < GSB_POSE_CLUSTER; ++r) v += cred[r][k];
         g[k] = v;
     }
     // g[0..8] = d/dR_wc (row-major), g[9..11] = d/dt_wc
@@ -199,7 +222,7 @@ void launch_pose_begin(int C, const gsb_pose_state* state, float* viewmats, cuda
 void launch_pose_finish(int C, int n_tiles, int n_loss_blocks, const float* partials, const float* loss_partials,
                         float* viewmats, gsb_pose_state* state, int* stop, gsb_tracker_config cfg,
                         float inv_pixels, float inv_rows3, float* history, int history_cap, cudaStream_t st) {
-    pose_finish_kernel<<<C, POSE_FINISH_THREADS, 0, st>>>(C, n_tiles, n_loss_blocks, partials, loss_partials, viewmats, state, stop,
+    pose_finish_kernel<<<C * GSB_POSE_CLUSTER, POSE_FINISH_THREADS, 0, st>>>(C, n_tiles, n_loss_blocks, partials, loss_partials, viewmats, state, stop,
                                           cfg, inv_pixels, inv_rows3, history, history_cap);
 }
 
