@@ -89,19 +89,41 @@ class SequenceResult:
 
 
 def track_frames(frame_ids: Sequence[int], load_frame, tracker, rank: int = 0, n_iters: Optional[int] = None,
-                 poll_every: int = 25) -> SequenceResult:
+                 poll_every: int = 25, chain: Optional[str] = None) -> SequenceResult:
     """Optimise the given frames one after another on ``tracker`` (a ``PoseTracker`` with C = 1), the way
     ``Runner.train`` walks the parser.  ``load_frame(i)`` returns a dict with ``means, quats, scales, opacities``
     (map of frame i+1 in its own coordinates), ``depth`` (observation of frame i), ``K``, ``c2w_init`` (ground-truth
-    pose of frame i+1's predecessor protocol, gs_trainer_total.py:63) and optionally ``c2w_gt``."""
+    pose of frame i+1's predecessor protocol, gs_trainer_total.py:63) and optionally ``c2w_gt``.
+
+    ``chain`` = ``"last"`` or ``"cv"`` turns the walk into odometry over ``frame_ids`` (consecutive frames):
+    ``load_frame(i, c2w_map)`` is then called with the TRACKED pose of the previous loop (``None`` for the first frame,
+    whose ``c2w_init`` starts the chain) and places the map there; the loop starts at that pose (``"last"``) or at the
+    constant-velocity prediction of ``motion.ConstantVelocity`` (``"cv"``, model.py:41-77)."""
+    if chain not in (None, "last", "cv"):
+        raise ValueError(f"chain must be None, 'last' or 'cv', not {chain!r}")
     rows, iters, ms = [], 0, 0.0
+    est = cv = None
     for f in frame_ids:
-        fr = load_frame(f)
+        fr = load_frame(f, est) if chain else load_frame(f)
+        init = fr["c2w_init"]
+        if chain:
+            if est is None:
+                from .motion import ConstantVelocity
+                est = np.asarray(fr["c2w_init"], dtype=np.float32).reshape(4, 4)
+                cv = ConstantVelocity(est)
+            init = cv.c2w() if chain == "cv" else est
         tracker.set_map(fr["means"], fr["quats"], fr["scales"], fr["opacities"])
         tracker.set_observation(fr["depth"], fr["K"])
-        tracker.set_poses(fr["c2w_init"], fr.get("c2w_gt"))
+        tracker.set_poses(init, fr.get("c2w_gt"))
         r = tracker.run(n_iters, poll_every=poll_every, use_graph=True)
         iters += r["iters"]
         ms += r["elapsed_ms"]
-        rows.append(state_to_record(f, rank, tracker.states()[0]))
+        st = tracker.states()[0]
+        rows.append(state_to_record(f, rank, st))
+        if chain:
+            from .tracker import quat_t_to_c2w
+            est = quat_t_to_c2w(st["q"], st["t"]).astype(np.float32)
+            cv.update_pose(est)                    # the loop's result becomes the current pose ...
+            if chain == "cv":
+                cv.update_pose()                   # ... and the next loop starts at the prediction
     return SequenceResult(np.asarray(rows, dtype=np.float64).reshape(-1, RECORD_WIDTH), iters, ms)

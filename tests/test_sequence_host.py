@@ -151,3 +151,65 @@ def test_replica_reader_on_a_small_tree(tmp_path):
         ds.Replica("room0", input_folder=root)
     with pytest.raises(FileNotFoundError):
         ds.Replica("room7", input_folder=root)
+
+
+# ------------------------------------------------------------------------------------------------ chained walk
+class _StandInTracker:
+    """Host stand-in for PoseTracker (the chaining logic is host code): every loop "finds" the ground-truth pose plus
+    a fixed 1 mm offset along x, and records where it was started."""
+
+    def __init__(self):
+        self.inits, self.maps = [], []
+
+    def set_map(self, means, quats, scales, opacities):
+        self.maps.append(np.asarray(means))
+
+    def set_observation(self, depth, K):
+        pass
+
+    def set_poses(self, c2w_init, c2w_gt=None):
+        self.inits.append(np.asarray(c2w_init, dtype=np.float64).copy())
+        self._gt = np.asarray(c2w_gt, dtype=np.float64)
+
+    def run(self, n_iters, poll_every=25, use_graph=True):
+        return {"iters": 7, "elapsed_ms": 1.0}
+
+    def states(self):
+        q = motion.rotation_matrix_to_quaternion(self._gt[:3, :3])
+        t = self._gt[:3, 3].astype(np.float32) + np.array([1e-3, 0, 0], dtype=np.float32)
+        z = 0.0
+        return [dict(iter=7, stopped=1, loss=z, depth_loss=z, edge_loss=z, normal_loss=z, eT=1e-3, eR=z, best_loss=z,
+                     best_eT=z, best_eR=z, best_iter=0, q=q, t=t)]
+
+
+@pytest.mark.parametrize("chain", ["last", "cv"])
+def test_track_frames_chains_the_tracked_pose(chain):
+    from gsplatloc_b200 import sharding
+
+    def gt(i):                                     # uniform motion: 2 cm per frame along z
+        p = np.eye(4)
+        p[2, 3] = 0.02 * i
+        return p
+
+    seen = []
+
+    def load_frame(f, c2w_map):
+        seen.append(None if c2w_map is None else np.asarray(c2w_map, dtype=np.float64).copy())
+        return dict(means=np.zeros((1, 3)), quats=None, scales=None, opacities=None, depth=None, K=np.eye(3),
+                    c2w_init=gt(f), c2w_gt=gt(f + 1))
+
+    trk = _StandInTracker()
+    res = sharding.track_frames([3, 4, 5, 6], load_frame, trk, rank=0, chain=chain)
+    assert res.iters == 28 and res.records.shape == (4, sharding.RECORD_WIDTH)
+    assert seen[0] is None                                       # the chain starts at the first frame's own pose
+    off = np.array([1e-3, 0, 0])
+    for n, f in enumerate([4, 5, 6], start=1):                   # later maps sit at the TRACKED pose of the loop before
+        np.testing.assert_allclose(seen[n][:3, 3], gt(f)[:3, 3] + off, atol=1e-6)
+    np.testing.assert_allclose(trk.inits[0], gt(3), atol=1e-7)
+    if chain == "last":
+        np.testing.assert_allclose(trk.inits[2][:3, 3], gt(5)[:3, 3] + off, atol=1e-6)
+    else:                                                        # uniform motion is extrapolated exactly from loop 3 on
+        np.testing.assert_allclose(trk.inits[2][:3, 3], gt(6)[:3, 3] + off, atol=1e-6)
+        np.testing.assert_allclose(trk.inits[3][:3, 3], gt(7)[:3, 3] + off, atol=1e-6)
+    with pytest.raises(ValueError):
+        sharding.track_frames([0], load_frame, trk, chain="slerp")
