@@ -346,7 +346,8 @@ __device__ void bitonic_sort(uint64_t* a, int n, bool smem) {
     }
 }
 
-// Register-resident variant for bins of at most 256 * K keys (K = 2: the usual ~300-key bins of a depth lattice):
+// Register-resident variant for bins of at most 256 * K keys (K = 1, 2, 4; K = 2: the usual ~300-key bins of a depth
+// lattice; K = 1 for bins of at most 256 keys, where K = 2 would spend half of every round on +inf padding):
 // thread t owns elements K*t .. K*t+K-1 of the (virtually +inf padded) array.  Every round of the network pairs element
 // i with i ^ m (flip of a block h: m = h - 1; disperse at distance d: m = d), so a round is
 //   m < K        : compare-exchange inside the thread's registers,
@@ -357,7 +358,7 @@ __device__ void bitonic_sort(uint64_t* a, int n, bool smem) {
 template <int K>
 __device__ __forceinline__ void reg_sort_round(uint64_t (&v)[K], int m, bool flip, int tid, int lane, uint64_t* sbuf,
                                                int& parity) {
-    constexpr int LGK = (K == 2) ? 1 : ((K == 4) ? 2 : 3);
+    constexpr int LGK = (K == 1) ? 0 : ((K == 2) ? 1 : ((K == 4) ? 2 : 3));
     if (m < K) {
 #pragma unroll
         for (int mm = 1; mm < K; ++mm)
@@ -405,7 +406,7 @@ template <int K>
 __device__ __forceinline__ void reg_tile_sort(const uint64_t* __restrict__ g, int n, uint64_t* sbuf, int start,
                                               int* __restrict__ flatten_ids, int64_t* __restrict__ isect_ids,
                                               int64_t hi) {
-    constexpr int LGP = 8 + ((K == 2) ? 1 : ((K == 4) ? 2 : 3));
+    constexpr int LGP = 8 + ((K == 1) ? 0 : ((K == 2) ? 1 : ((K == 4) ? 2 : 3)));
     const int tid = threadIdx.x, lane = tid & 31;
     uint64_t v[K];
 #pragma unroll
@@ -443,6 +444,7 @@ __global__ void __launch_bounds__(256) tile_sort_kernel(int n_tiles, int tile_bi
     if (n <= 0) return;
     uint64_t* g = keys + start;
     const int64_t hi = ((int64_t)cam << (32 + tile_bits)) | ((int64_t)(bin % n_tiles) << 32);
+    if (n <= 256) { reg_tile_sort<1>(g, n, sk, start, flatten_ids, isect_ids, hi); return; }   // half the work per round
     if (n <= 512) { reg_tile_sort<2>(g, n, sk, start, flatten_ids, isect_ids, hi); return; }
     if (n <= 1024) { reg_tile_sort<4>(g, n, sk, start, flatten_ids, isect_ids, hi); return; }
     uint64_t* a = g;
@@ -481,6 +483,7 @@ __global__ void __launch_bounds__(256) tile_sort_fixed_kernel(int n_tiles, int t
     }
     if (n <= 0) return;
     uint64_t* g = keys + start;
+    if (n <= 256) { reg_tile_sort<1>(g, n, sk, start, flatten_ids, nullptr, 0); return; }
     if (n <= 512) { reg_tile_sort<2>(g, n, sk, start, flatten_ids, nullptr, 0); return; }
     if (n <= 1024) { reg_tile_sort<4>(g, n, sk, start, flatten_ids, nullptr, 0); return; }
     uint64_t* a = g;
