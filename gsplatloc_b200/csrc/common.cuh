@@ -234,6 +234,22 @@ __device__ __forceinline__ float rcp_fast(float x) {
     return y;
 }
 
+
+// ---- Blackwell packed fp32 (sm_100: fma.rn.f32x2 / mul.f32x2 / add.f32x2 -> FFMA2 / FMUL2 / FADD2).  One issue slot
+// for two IEEE-rn results, bit-identical to the scalar instructions; measured on B200 (tools/microbench.cu,
+// profiles/r2_microbench.jsonl) the fma pipe takes two cycles for a packed instruction, so packing buys issue slots,
+// not flops -- which is what the raster kernels are short of.
+typedef float2 f2;
+__device__ __forceinline__ f2 f2mul(f2 a, f2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ f2 f2add(f2 a, f2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ f2 f2fma(f2 a, f2 b, f2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ f2 f2s(float s) { return make_float2(s, s); }
+__device__ __forceinline__ float ex2_fast(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

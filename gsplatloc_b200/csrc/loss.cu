@@ -97,15 +97,40 @@ __global__ void __launch_bounds__(256) normal_rowsum_kernel(int W, int H, const 
     }
 }
 
+// E(gt) of the whole observation, once per frame (tracker: set_observation): the loss kernel recomputed it every
+// iteration although gt is constant; it is reused wherever the mask d != 0 is all ones around a block.
+__global__ void __launch_bounds__(256) edge_magnitude_kernel(int W, int H, const float* __restrict__ img,
+                                                             float* __restrict__ out) {
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= W || y >= H) return;
+    const int xm = max(x - 1, 0), xp = min(x + 1, W - 1), ym = max(y - 1, 0), yp = min(y + 1, H - 1);
+    const float b00 = img[(size_t)ym * W + xm], b01 = img[(size_t)ym * W + x], b02 = img[(size_t)ym * W + xp];
+    const float b10 = img[(size_t)y * W + xm], b12 = img[(size_t)y * W + xp];
+    const float b20 = img[(size_t)yp * W + xm], b21 = img[(size_t)yp * W + x], b22 = img[(size_t)yp * W + xp];
+    const float gx = ((b02 - b00) + 2.f * (b12 - b10) + (b22 - b20)) * 0.125f;
+    const float gy = ((b20 - b00) + 2.f * (b21 - b01) + (b22 - b02)) * 0.125f;
+    out[(size_t)y * W + x] = sqrtf(gx * gx + gy * gy + 1e-6f);
+}
+
+void launch_edge_magnitude(int W, int H, const float* img, float* out, cudaStream_t st) {
+    if (W * H == 0) return;
+    edge_magnitude_kernel<<<dim3((W + 31) / 32, (H + 7) / 8), 256, 0, st>>>(W, H, img, out);
+}
+
 // NMODE: 0 = no normal term, 1 = per-pixel cosine (dim=-1), 2 = reference-faithful cosine over the image width
 // (dim=1; needs the row sums of normal_rowsum_kernel).  w_n = lambda_n / (H*W) (mode 1) or lambda_n / (3*H) (mode 2).
 // Block partials: {sum|A-B|, sum|E(A)-E(B)|, sum cos} (3 floats per block).
+// ``gt_edge`` (nullable): E(gt) of the unmasked observation (edge_magnitude_kernel).  A block whose halo-2 window holds
+// no d == 0 sees B = gt there, so E(B) is read instead of recomputed and B's halo is never staged; a block with a hole
+// (or a caller without the cache) takes the exact masked recomputation.  On the rendered side sqrt and the division
+// by E(A) are ONE rsqrt: s = gx^2 + gy^2 + 1e-6, r = rsqrt(s), E(A) = s r, w_s sgn / E(A) = w_s sgn r.
 template <int NMODE>
 __global__ void __launch_bounds__(LBX* LBY) loss_kernel(
     int C, int W, int H, const float* __restrict__ ed, const float* __restrict__ alpha,
     const float* __restrict__ gt, size_t gt_cam_stride, int apply_mask, float w_d, float w_s, float w_n,
     const float* __restrict__ Ks, const float* __restrict__ rows, int mode, float* __restrict__ v_out,
-    float* __restrict__ v_alpha, float* __restrict__ partial, const int* __restrict__ stop) {
+    float* __restrict__ v_alpha, float* __restrict__ partial, const int* __restrict__ stop,
+    const float* __restrict__ gt_edge) {
     __shared__ float sA[LH][LW], sB[LH][LW];
     __shared__ float sKx[LBY + 2][LBX + 2], sKy[LBY + 2][LBX + 2];
     __shared__ float sHn[NMODE ? 6 : 1][LBY + 2][LBX + 2];   // Hx = dy x G, Hy = G x dx of the halo-1 window
@@ -122,44 +147,66 @@ __global__ void __launch_bounds__(LBX* LBY) loss_kernel(
         ifx = 1.f / K[0]; ify = 1.f / K[4]; cx = K[2]; cy = K[5];
     }
 
+    // ---- stage the halo-2 window of A (= d); note whether it holds a masked pixel
+    int hole = 0;
     for (int q = tid; q < LH * LW; q += LBX * LBY) {
-        int r = q / LW, c = q % LW;
-        int y = min(max(y0 + r - 2, 0), H - 1), x = min(max(x0 + c - 2, 0), W - 1);
-        float d = d_img[(size_t)y * W + x];
-        float g = g_img[(size_t)y * W + x];
+        const int r = q / LW, c = q - r * LW;
+        const int y = min(max(y0 + r - 2, 0), H - 1), x = min(max(x0 + c - 2, 0), W - 1);
+        const float d = d_img[(size_t)y * W + x];
         sA[r][c] = d;
-        sB[r][c] = apply_mask ? ((d != 0.f) ? g : 0.f) : g;
+        hole |= (d == 0.f) ? 1 : 0;
     }
-    __syncthreads();
+    const bool masked = apply_mask && __syncthreads_or(hole);          // (a barrier either way)
+    if (!apply_mask) __syncthreads();
+    // B's window is needed by the normal term and wherever E(B) has to be recomputed
+    const bool cached = gt_edge && !masked;
+    const bool stage_b = NMODE != 0 || !cached;
+    if (stage_b) {
+        for (int q = tid; q < LH * LW; q += LBX * LBY) {
+            const int r = q / LW, c = q - r * LW;
+            const int y = min(max(y0 + r - 2, 0), H - 1), x = min(max(x0 + c - 2, 0), W - 1);
+            const float g = g_img[(size_t)y * W + x];
+            sB[r][c] = (apply_mask && sA[r][c] == 0.f) ? 0.f : g;
+        }
+        __syncthreads();
+    }
 
     float sum_d = 0.f, sum_s = 0.f, sum_n = 0.f;
     for (int q = tid; q < (LBY + 2) * (LBX + 2); q += LBX * LBY) {
-        int r = q / (LBX + 2), c = q % (LBX + 2);
-        int y = y0 + r - 1, x = x0 + c - 1;
+        const int r = q / (LBX + 2), c = q - r * (LBX + 2);
+        const int y = y0 + r - 1, x = x0 + c - 1;
         float kx = 0.f, ky = 0.f;
         float hn[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         if (y >= 0 && y < H && x >= 0 && x < W) {
             // window centre in smem coordinates
-            int sr = r + 1, sc = c + 1;
+            const int sr = r + 1, sc = c + 1;
             const bool own = (r >= 1 && r <= LBY && c >= 1 && c <= LBX);  // this block's own pixel
-            float a00 = sA[sr - 1][sc - 1], a01 = sA[sr - 1][sc], a02 = sA[sr - 1][sc + 1];
-            float a10 = sA[sr][sc - 1], a12 = sA[sr][sc + 1];
-            float a20 = sA[sr + 1][sc - 1], a21 = sA[sr + 1][sc], a22 = sA[sr + 1][sc + 1];
-            float gxA = ((a02 - a00) + 2.f * (a12 - a10) + (a22 - a20)) * 0.125f;
-            float gyA = ((a20 - a00) + 2.f * (a21 - a01) + (a22 - a02)) * 0.125f;
-            float EA = sqrtf(gxA * gxA + gyA * gyA + 1e-6f);
-            float b00 = sB[sr - 1][sc - 1], b01 = sB[sr - 1][sc], b02 = sB[sr - 1][sc + 1];
-            float b10 = sB[sr][sc - 1], b12 = sB[sr][sc + 1];
-            float b20 = sB[sr + 1][sc - 1], b21 = sB[sr + 1][sc], b22 = sB[sr + 1][sc + 1];
-            float gxB = ((b02 - b00) + 2.f * (b12 - b10) + (b22 - b20)) * 0.125f;
-            float gyB = ((b20 - b00) + 2.f * (b21 - b01) + (b22 - b02)) * 0.125f;
-            float EB = sqrtf(gxB * gxB + gyB * gyB + 1e-6f);
-            float k = w_s * sgn(EA - EB) / EA;
-            kx = k * gxA; ky = k * gyA;
-            if (own) {
-                sum_s += fabsf(EA - EB);
-                sum_d += fabsf(sA[sr][sc] - sB[sr][sc]);
+            const float a00 = sA[sr - 1][sc - 1], a01 = sA[sr - 1][sc], a02 = sA[sr - 1][sc + 1];
+            const float a10 = sA[sr][sc - 1], a12 = sA[sr][sc + 1];
+            const float a20 = sA[sr + 1][sc - 1], a21 = sA[sr + 1][sc], a22 = sA[sr + 1][sc + 1];
+            const float gxA = ((a02 - a00) + 2.f * (a12 - a10) + (a22 - a20)) * 0.125f;
+            const float gyA = ((a20 - a00) + 2.f * (a21 - a01) + (a22 - a02)) * 0.125f;
+            const float sq = fmaf(gxA, gxA, fmaf(gyA, gyA, 1e-6f));
+            const float rs = rsqrtf(sq);
+            const float EA = sq * rs;
+            float EB;
+            float b10 = 0.f, b12 = 0.f, b01 = 0.f, b21 = 0.f;
+            if (stage_b) {
+                b10 = sB[sr][sc - 1]; b12 = sB[sr][sc + 1]; b01 = sB[sr - 1][sc]; b21 = sB[sr + 1][sc];
             }
+            if (cached) {
+                EB = gt_edge[(size_t)cam * gt_cam_stride + (size_t)y * W + x];
+            } else {
+                const float b00 = sB[sr - 1][sc - 1], b02 = sB[sr - 1][sc + 1];
+                const float b20 = sB[sr + 1][sc - 1], b22 = sB[sr + 1][sc + 1];
+                const float gxB = ((b02 - b00) + 2.f * (b12 - b10) + (b22 - b20)) * 0.125f;
+                const float gyB = ((b20 - b00) + 2.f * (b21 - b01) + (b22 - b02)) * 0.125f;
+                EB = sqrtf(gxB * gxB + gyB * gyB + 1e-6f);
+            }
+            const float diff = EA - EB;
+            const float k = (diff == 0.f) ? 0.f : copysignf(w_s * rs, diff);   // w_s sgn(E(A) - E(B)) / E(A)
+            kx = k * gxA; ky = k * gyA;
+            if (own) sum_s += fabsf(diff);
             if (NMODE) {
                 const int xm = max(x - 1, 0), xp = min(x + 1, W - 1), ym = max(y - 1, 0), yp = min(y + 1, H - 1);
                 const float rx = ((float)x - cx) * ifx, rxm = ((float)xm - cx) * ifx, rxp = ((float)xp - cx) * ifx;
@@ -177,11 +224,11 @@ __global__ void __launch_bounds__(LBX* LBY) loss_kernel(
 #pragma unroll
                     for (int k3 = 0; k3 < 3; ++k3) gn[k3] = -w_n * (nB.n[k3] * ia * ib - cosv * nA.n[k3] * ia * ia);
                 } else {
-                    const float* rs = rows + ((size_t)cam * H + y) * 9;
+                    const float* rs9 = rows + ((size_t)cam * H + y) * 9;
 #pragma unroll
                     for (int k3 = 0; k3 < 3; ++k3) {
-                        const float ia = 1.f / fmaxf(sqrtf(rs[3 + k3]), 1e-8f), ib = 1.f / fmaxf(sqrtf(rs[6 + k3]), 1e-8f);
-                        const float cosv = rs[k3] * ia * ib;
+                        const float ia = 1.f / fmaxf(sqrtf(rs9[3 + k3]), 1e-8f), ib = 1.f / fmaxf(sqrtf(rs9[6 + k3]), 1e-8f);
+                        const float cosv = rs9[k3] * ia * ib;
                         gn[k3] = -w_n * (nB.n[k3] * ia * ib - cosv * nA.n[k3] * ia * ia);
                     }
                 }
@@ -214,8 +261,8 @@ __global__ void __launch_bounds__(LBX* LBY) loss_kernel(
     if (NMODE == 2 && blockIdx.x == 0 && tid < LBY * 3) {   // this block's rows: sum of the per-(row, channel) cosines
         const int y = y0 + tid / 3, k3 = tid % 3;
         if (y < H) {
-            const float* rs = rows + ((size_t)cam * H + y) * 9;
-            sum_n += rs[k3] / (fmaxf(sqrtf(rs[3 + k3]), 1e-8f) * fmaxf(sqrtf(rs[6 + k3]), 1e-8f));
+            const float* rs9 = rows + ((size_t)cam * H + y) * 9;
+            sum_n += rs9[k3] / (fmaxf(sqrtf(rs9[3 + k3]), 1e-8f) * fmaxf(sqrtf(rs9[6 + k3]), 1e-8f));
         }
     }
     __syncthreads();
@@ -225,17 +272,17 @@ __global__ void __launch_bounds__(LBX* LBY) loss_kernel(
         const int sr = threadIdx.y + 2, sc = threadIdx.x + 2;     // in sA/sB
         const int kr = threadIdx.y + 1, kc = threadIdx.x + 1;     // in sKx/sKy
         const float a = sA[sr][sc];
-        float v = w_d * sgn(a - sB[sr][sc]);
+        const float g_own = stage_b ? sB[sr][sc] : g_img[(size_t)y * W + x];   // (no hole in the window: B = gt)
+        sum_d += fabsf(a - g_own);
+        float v = w_d * sgn(a - g_own);
         if (x >= 1 && x <= W - 2 && y >= 1 && y <= H - 2) {
-            // interior: pixel q receives from p = q - o with weight K(o); Kx(oy,ox) = ox (2-|oy|)/8
-#pragma unroll
-            for (int oy = -1; oy <= 1; ++oy)
-#pragma unroll
-                for (int ox = -1; ox <= 1; ++ox) {
-                    float wx = (float)(ox * (2 - (oy < 0 ? -oy : oy))) * 0.125f;
-                    float wy = (float)(oy * (2 - (ox < 0 ? -ox : ox))) * 0.125f;
-                    v += sKx[kr - oy][kc - ox] * wx + sKy[kr - oy][kc - ox] * wy;
-                }
+            // interior: pixel q receives from p = q - o with weight K(o); Kx(oy,ox) = ox (2-|oy|)/8 is zero in the
+            // middle column and Ky(oy,ox) = oy (2-|ox|)/8 in the middle row: 6 + 6 taps
+            float vx = sKx[kr][kc - 1] - sKx[kr][kc + 1];
+            vx = fmaf(2.f, vx, sKx[kr - 1][kc - 1] - sKx[kr - 1][kc + 1]) + (sKx[kr + 1][kc - 1] - sKx[kr + 1][kc + 1]);
+            float vy = sKy[kr - 1][kc] - sKy[kr + 1][kc];
+            vy = fmaf(2.f, vy, sKy[kr - 1][kc - 1] - sKy[kr + 1][kc - 1]) + (sKy[kr - 1][kc + 1] - sKy[kr + 1][kc + 1]);
+            v = fmaf(0.125f, vx + vy, v);
         } else {
             // border: replicate padding folds out-of-range taps back onto this pixel
             for (int py = -1; py <= 1; ++py)
@@ -274,13 +321,14 @@ __global__ void __launch_bounds__(LBX* LBY) loss_kernel(
         } else {
             const float al = alpha[pix];
             const float ac = fmaxf(al, 1e-10f);
-            v_out[pix] = v / ac;
-            v_alpha[pix] = (al >= 1e-10f) ? -v * a / ac : 0.f;
+            const float vq = __fdividef(v, ac);
+            v_out[pix] = vq;
+            v_alpha[pix] = (al >= 1e-10f) ? -vq * a : 0.f;
         }
     }
 
     // block partial sums (fixed order)
-    float sd = warp_sum(sum_d), ss = warp_sum(sum_s), sn = warp_sum(sum_n);
+    float sd = warp_sum(sum_d), ss = warp_sum(sum_s), sn = NMODE ? warp_sum(sum_n) : 0.f;
     if ((tid & 31) == 0) { s_red[0][tid >> 5] = sd; s_red[1][tid >> 5] = ss; s_red[2][tid >> 5] = sn; }
     __syncthreads();
     if (tid < 3) {
@@ -302,7 +350,7 @@ void loss_grid(int W, int H, int* gx, int* gy) {
 void launch_loss(int C, int W, int H, const float* ed, const float* alpha, const float* gt, size_t gt_cam_stride,
                  int apply_mask, float w_d, float w_s, float lambda_n, int normal_mode, const float* Ks,
                  float* normal_rows, int mode, float* v_out, float* v_alpha, float* partial, const int* stop,
-                 cudaStream_t st) {
+                 const float* gt_edge, cudaStream_t st) {
     if (C * W * H == 0) return;
     int gx, gy;
     loss_grid(W, H, &gx, &gy);
@@ -312,14 +360,14 @@ void launch_loss(int C, int W, int H, const float* ed, const float* alpha, const
         normal_rowsum_kernel<<<dim3(H, C), 256, 0, st>>>(W, H, ed, gt, gt_cam_stride, apply_mask, Ks, normal_rows, stop);
         loss_kernel<2><<<grid, block, 0, st>>>(C, W, H, ed, alpha, gt, gt_cam_stride, apply_mask, w_d, w_s,
                                                lambda_n / (3.f * (float)H), Ks, normal_rows, mode, v_out, v_alpha,
-                                               partial, stop);
+                                               partial, stop, gt_edge);
     } else if (normal_mode == 1) {
         loss_kernel<1><<<grid, block, 0, st>>>(C, W, H, ed, alpha, gt, gt_cam_stride, apply_mask, w_d, w_s,
                                                lambda_n / ((float)W * (float)H), Ks, nullptr, mode, v_out, v_alpha,
-                                               partial, stop);
+                                               partial, stop, gt_edge);
     } else {
         loss_kernel<0><<<grid, block, 0, st>>>(C, W, H, ed, alpha, gt, gt_cam_stride, apply_mask, w_d, w_s, 0.f,
-                                               nullptr, nullptr, mode, v_out, v_alpha, partial, stop);
+                                               nullptr, nullptr, mode, v_out, v_alpha, partial, stop, gt_edge);
     }
 }
 

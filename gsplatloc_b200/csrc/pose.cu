@@ -81,6 +81,9 @@ __global__ void __cluster_dims__(GSB_POSE_CLUSTER, 1, 1) __launch_bounds__(POSE_
     const int rank = (int)cluster.block_rank();
     const int c = blockIdx.x / GSB_POSE_CLUSTER, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     if (state[c].stopped) return;                  // the same answer in every block of the cluster
+    // Distributed shared memory may only be touched once its owner block is known to run: every block arrives here and
+    // waits just before its remote store below, so the barrier's latency hides behind the global-memory sums.
+    cluster.barrier_arrive();
     // fixed-order sums: 12 pose-gradient numbers over tiles, 3 loss sums over loss blocks
     float acc[15];
 #pragma unroll
@@ -109,6 +112,7 @@ __global__ void __cluster_dims__(GSB_POSE_CLUSTER, 1, 1) __launch_bounds__(POSE_
         if (lane == 0) red[k][wid] = v;
     }
     __syncthreads();
+    cluster.barrier_wait();                        // every block of the cluster has started: its shared memory exists
     if (tid < 15) {
         float v = 0.f;
 #pragma unroll

@@ -1,5 +1,5 @@
 // Device-resident pose-optimisation runtime: owns the buffers of one frame (Gaussians, observation, C pose
-// hypotheses), enqueues the nine kernels of an iteration, replays them as a CUDA graph and polls the early-stop
+// hypotheses), enqueues the six kernels of an iteration, replays them as a CUDA graph and polls the early-stop
 // flag.  This is the B200 twin of the inner loop of Runner.train (src/my_gsplat/gs_trainer_total.py:78-267): no
 // autograd graph, no per-step host synchronisation, no allocation inside the loop.
 #include <math.h>
@@ -33,6 +33,7 @@ struct gsb_tracker {
     gsb_tracker_config cfg;
     float *means = nullptr, *quats = nullptr, *scales = nullptr, *opac = nullptr;
     float *gt = nullptr, *Ks = nullptr, *viewmats = nullptr;
+    float* gt_edge = nullptr;   // Sobel magnitude of the observation, once per frame (loss.cu edge_magnitude_kernel)
     gsb_pose_state* state = nullptr;
     gsb_pose_state* state_bak = nullptr;   // poses at the start of the current run (restored when a bin overflows)
     float* viewmats_bak = nullptr;
@@ -101,7 +102,7 @@ static void enqueue_iteration(gsb_tracker* t, bool forward_only, cudaEvent_t* ma
     const float inv_p = 1.f / ((float)t->W * (float)t->H);
     launch_loss(C, t->W, t->H, t->ed, t->alpha, t->gt, 0, 1, c.depth_lambda * inv_p,
                 (1.f - c.depth_lambda - c.normal_lambda) * inv_p, c.normal_lambda, c.normal_mode, t->Ks,
-                t->normal_rows, 1, t->v_depth, t->v_alpha, t->loss_partials, t->stop, st);
+                t->normal_rows, 1, t->v_depth, t->v_alpha, t->loss_partials, t->stop, t->gt_edge, st);
     GSB_MARK();
     launch_raster_bwd_lift(C, N, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->ranges, t->flatten_ids,
                            t->alpha, t->last_ids, t->v_depth, t->v_alpha, t->means, t->quats, t->scales, t->viewmats,
@@ -123,12 +124,15 @@ static int resize_bins(gsb_tracker* t, int want_cap) {
     if (t->flatten_ids) cudaFree(t->flatten_ids);
     if (t->masks) cudaFree(t->masks);
     t->keys = nullptr; t->flatten_ids = nullptr; t->masks = nullptr;
+    // (a failed allocation below leaves no bins: the next run sizes them again instead of launching on null buffers)
+    t->cap = 0; t->tile_cap = 0; t->cap_dirty = true;
+    invalidate_graph(t);
     TCK(cudaMalloc(&t->keys, sizeof(uint64_t) * (size_t)want), "alloc keys");
     TCK(cudaMalloc(&t->flatten_ids, sizeof(int) * (size_t)want), "alloc flatten_ids");
     TCK(cudaMalloc(&t->masks, (size_t)want), "alloc masks");
     t->cap = want;
     t->tile_cap = want_cap;
-    invalidate_graph(t);
+    t->cap_dirty = false;   // (both callers have just run the counting pass at the current poses)
     return GSB_OK;
 }
 
@@ -194,11 +198,10 @@ void gsb_tracker_default_config(gsb_tracker_config* cfg, int max_steps) {
     cfg->normal_mode = GSB_NORMAL_REFERENCE;
 }
 
-int gsb_tracker_create(gsb_tracker** out, int C, int W, int H, void* stream) {
-    if (!out || C <= 0 || W <= 0 || H <= 0) return fail(GSB_ERR_ARG, "gsb_tracker_create: bad sizes", cudaSuccess);
-    int dev_count = 0;
-    TCK(cudaGetDeviceCount(&dev_count), "gsb_tracker_create: no CUDA device");
-    gsb_tracker* t = new gsb_tracker();
+void gsb_tracker_destroy(gsb_tracker* t);
+
+// every allocation of a tracker; on failure the caller destroys the half-built object (nothing leaks)
+static int tracker_alloc(gsb_tracker* t, int C, int W, int H, void* stream) {
     t->C = C; t->W = W; t->H = H;
     t->tile_w = (W + GSB_TILE - 1) / GSB_TILE; t->tile_h = (H + GSB_TILE - 1) / GSB_TILE;
     t->n_tiles = t->tile_w * t->tile_h;
@@ -212,6 +215,7 @@ int gsb_tracker_create(gsb_tracker** out, int C, int W, int H, void* stream) {
     t->n_loss_blocks = gx * gy;
     t->history_cap = 4096;
     TCK(cudaMalloc(&t->gt, sizeof(float) * (size_t)W * H), "alloc");
+    TCK(cudaMalloc(&t->gt_edge, sizeof(float) * (size_t)W * H), "alloc");
     TCK(cudaMalloc(&t->Ks, sizeof(float) * 9 * C), "alloc");
     TCK(cudaMalloc(&t->viewmats, sizeof(float) * 16 * C), "alloc");
     TCK(cudaMalloc(&t->state, sizeof(gsb_pose_state) * C), "alloc");
@@ -244,6 +248,21 @@ int gsb_tracker_create(gsb_tracker** out, int C, int W, int H, void* stream) {
     TCK(cudaMemsetAsync(t->partials, 0, sizeof(float) * nb * 12 * raster_bwd_partials_per_tile(), t->stream), "memset");
     TCK(cudaEventCreate(&t->ev0), "event");
     TCK(cudaEventCreate(&t->ev1), "event");
+    return GSB_OK;
+}
+
+int gsb_tracker_create(gsb_tracker** out, int C, int W, int H, void* stream) {
+    if (!out || C <= 0 || W <= 0 || H <= 0) return fail(GSB_ERR_ARG, "gsb_tracker_create: bad sizes", cudaSuccess);
+    int dev_count = 0;
+    TCK(cudaGetDeviceCount(&dev_count), "gsb_tracker_create: no CUDA device");
+    gsb_tracker* t = new gsb_tracker();
+    const int rc = tracker_alloc(t, C, W, H, stream);
+    if (rc) {
+        const std::string why = g_err;   // (destroy must not overwrite the reason)
+        gsb_tracker_destroy(t);
+        g_err = why;
+        return rc;
+    }
     *out = t;
     return GSB_OK;
 }
@@ -252,7 +271,7 @@ void gsb_tracker_destroy(gsb_tracker* t) {
     if (!t) return;
     cudaStreamSynchronize(t->stream);
     invalidate_graph(t);
-    void* bufs[] = {t->means, t->quats, t->scales, t->opac, t->gt, t->Ks, t->viewmats, t->state, t->stop, t->rec,
+    void* bufs[] = {t->means, t->quats, t->scales, t->opac, t->gt, t->gt_edge, t->Ks, t->viewmats, t->state, t->stop, t->rec,
                     t->bbox, t->counts, t->offsets, t->cursor, t->ranges, t->n_isects, t->keys, t->flatten_ids, t->masks, t->ed, t->alpha,
                     t->v_depth, t->v_alpha, t->last_ids, t->partials, t->loss_partials, t->normal_rows,
                     t->history, t->state_bak, t->viewmats_bak, t->stop_bak};
@@ -307,6 +326,7 @@ int gsb_tracker_set_observation(gsb_tracker* t, const float* depth, int on_host,
     if (!t || !depth || !K_host) return fail(GSB_ERR_ARG, "gsb_tracker_set_observation: null", cudaSuccess);
     TCK(cudaMemcpyAsync(t->gt, depth, sizeof(float) * (size_t)t->W * t->H,
                         on_host ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, t->stream), "copy depth");
+    launch_edge_magnitude(t->W, t->H, t->gt, t->gt_edge, t->stream);
     std::vector<float> ks((size_t)t->C * 9);
     for (int c = 0; c < t->C; ++c) memcpy(ks.data() + c * 9, K_host, sizeof(float) * 9);
     TCK(cudaMemcpyAsync(t->Ks, ks.data(), sizeof(float) * ks.size(), cudaMemcpyHostToDevice, t->stream), "copy K");

@@ -64,9 +64,12 @@ class _FullyFusedProjection(torch.autograd.Function):
         v_scales = torch.zeros_like(scales) if need[2] else None
         v_view = torch.zeros_like(viewmats) if need[3] else None
         if any(need[:4]):
+            # contiguous copies are bound to names: a temporary would be freed (and its block possibly reused by the
+            # next temporary) before the kernel that reads it is enqueued
+            vm2, vdp, vcn = v_means2d.contiguous(), v_depths.contiguous(), v_conics.contiguous()
             _lib.check(_lib.lib().gsb_projection_bwd(
                 Cn, N, _p(means), _p(quats), _p(scales), _p(viewmats), _p(Ks), width, height, eps2d, _p(radii),
-                _p(v_means2d.contiguous()), _p(v_depths.contiguous()), _p(v_conics.contiguous()), _p(v_means),
+                _p(vm2), _p(vdp), _p(vcn), _p(v_means),
                 _p(v_quats), _p(v_scales), _p(v_view), _stream()), "projection_bwd")
         return v_means, v_quats, v_scales, v_view, None, None, None, None, None, None, None
 
@@ -164,10 +167,11 @@ class _RasterizeToPixels(torch.autograd.Function):
         Cn, N, D = colors.shape
         v_means2d, v_conics = torch.zeros_like(means2d), torch.zeros_like(conics)
         v_colors, v_opac = torch.zeros_like(colors), torch.zeros_like(opacities)
+        vrc, vra = v_render_colors.contiguous(), v_render_alphas.contiguous()   # named: alive until the launch
         _lib.check(_lib.lib().gsb_rasterize_bwd(
             Cn, N, D, _p(means2d), _p(conics), _p(colors), _p(opacities), _p(backgrounds), width, height, tile_size,
             _p(isect_offsets), _p(flatten_ids), flatten_ids.numel(), _p(render_alphas), _p(last_ids),
-            _p(v_render_colors.contiguous()), _p(v_render_alphas.contiguous()), _p(v_means2d), _p(v_conics),
+            _p(vrc), _p(vra), _p(v_means2d), _p(v_conics),
             _p(v_colors), _p(v_opac), _stream()), "rasterize_bwd")
         v_bg = None
         if backgrounds is not None and ctx.needs_input_grad[4]:
@@ -221,8 +225,9 @@ class _SphericalHarmonics(torch.autograd.Function):
         n, K = dirs.shape[0], coeffs.shape[1]
         v_coeffs = torch.zeros_like(coeffs)
         v_dirs = torch.zeros_like(dirs) if ctx.needs_input_grad[1] else None
+        vcol = v_colors.contiguous()   # named: alive until the launch
         _lib.check(_lib.lib().gsb_sh_bwd(n, K, ctx.degree, _p(dirs), _p(coeffs), _p(masks),
-                                         _p(v_colors.contiguous()), _p(v_coeffs), _p(v_dirs), _stream()), "sh_bwd")
+                                         _p(vcol), _p(v_coeffs), _p(v_dirs), _stream()), "sh_bwd")
         return None, v_dirs, v_coeffs, None
 
 

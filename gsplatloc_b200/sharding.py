@@ -88,8 +88,21 @@ class SequenceResult:
     device_ms: float           # CUDA-event time of the tracker loops (setup excluded)
 
 
+def chained_pose(st: dict, use_best: bool = True):
+    """Pose a finished loop hands to the next one: the pose at the best-loss step when early stopping recorded one
+    (``update_pose``: "update with best pose after a train loop", model.py:41-48), else the last pose."""
+    if use_best and int(st.get("best_iter", -1)) >= 0:
+        return st["best_q"], st["best_t"]
+    return st["q"], st["t"]
+
+
+def state_iters(st: dict) -> int:
+    """Pose iterations a loop actually executed (graph launches after the stop flag are no-ops and not counted)."""
+    return int(st["iter"]) + (1 if st.get("stopped") else 0)
+
+
 def track_frames(frame_ids: Sequence[int], load_frame, tracker, rank: int = 0, n_iters: Optional[int] = None,
-                 poll_every: int = 25, chain: Optional[str] = None) -> SequenceResult:
+                 poll_every: int = 25, chain: Optional[str] = None, chain_best: bool = True) -> SequenceResult:
     """Optimise the given frames one after another on ``tracker`` (a ``PoseTracker`` with C = 1), the way
     ``Runner.train`` walks the parser.  ``load_frame(i)`` returns a dict with ``means, quats, scales, opacities``
     (map of frame i+1 in its own coordinates), ``depth`` (observation of frame i), ``K``, ``c2w_init`` (ground-truth
@@ -98,7 +111,8 @@ def track_frames(frame_ids: Sequence[int], load_frame, tracker, rank: int = 0, n
     ``chain`` = ``"last"`` or ``"cv"`` turns the walk into odometry over ``frame_ids`` (consecutive frames):
     ``load_frame(i, c2w_map)`` is then called with the TRACKED pose of the previous loop (``None`` for the first frame,
     whose ``c2w_init`` starts the chain) and places the map there; the loop starts at that pose (``"last"``) or at the
-    constant-velocity prediction of ``motion.ConstantVelocity`` (``"cv"``, model.py:41-77)."""
+    constant-velocity prediction of ``motion.ConstantVelocity`` (``"cv"``, model.py:41-77).  ``chain_best``: the pose
+    handed on is the one at the best-loss step (the reference's contract), not the one ``patience`` steps later."""
     if chain not in (None, "last", "cv"):
         raise ValueError(f"chain must be None, 'last' or 'cv', not {chain!r}")
     rows, iters, ms = [], 0, 0.0
@@ -116,13 +130,13 @@ def track_frames(frame_ids: Sequence[int], load_frame, tracker, rank: int = 0, n
         tracker.set_observation(fr["depth"], fr["K"])
         tracker.set_poses(init, fr.get("c2w_gt"))
         r = tracker.run(n_iters, poll_every=poll_every, use_graph=True)
-        iters += r["iters"]
         ms += r["elapsed_ms"]
         st = tracker.states()[0]
+        iters += state_iters(st) if "iter" in st else r["iters"]
         rows.append(state_to_record(f, rank, st))
         if chain:
             from .tracker import quat_t_to_c2w
-            est = quat_t_to_c2w(st["q"], st["t"]).astype(np.float32)
+            est = quat_t_to_c2w(*chained_pose(st, chain_best)).astype(np.float32)
             cv.update_pose(est)                    # the loop's result becomes the current pose ...
             if chain == "cv":
                 cv.update_pose()                   # ... and the next loop starts at the prediction

@@ -1,5 +1,5 @@
 """Device-resident pose optimisation: the inner loop of ``Runner.train``
-(``src/my_gsplat/gs_trainer_total.py:78-267``) for one frame pair and ``C`` pose hypotheses, run as nine
+(``src/my_gsplat/gs_trainer_total.py:78-267``) for one frame pair and ``C`` pose hypotheses, run as six
 hand-written kernels per iteration inside a CUDA graph (``csrc/tracker.cu``).  Host code only feeds buffers, polls
 the early-stop flag and reads the result back.
 """

@@ -137,14 +137,14 @@ def main():
                 est = frames[f]["c2w_tar"]
                 cv = motion.ConstantVelocity(est)
             st, r, ts, tl = track(frames[f], est, cv.c2w() if args.chain == "cv" else est)
-            est = quat_t_to_c2w(st["q"], st["t"]).astype(np.float32)
+            est = quat_t_to_c2w(*sharding.chained_pose(st)).astype(np.float32)   # the best-loss pose (model.py:41-48)
             cv.update_pose(est)                        # the loop's result becomes the current pose ...
             if args.chain == "cv":
                 cv.update_pose()                       # ... and the next loop starts at the prediction
         else:
             st, r, ts, tl = track(frames[f])
         rows.append(sharding.state_to_record(f, rank, st))
-        iters += r["iters"]; t_setup += ts; t_loop += tl
+        iters += sharding.state_iters(st); t_setup += ts; t_loop += tl
     torch.cuda.synchronize(dev)
     wall = time.perf_counter() - w0
     agg = torch.tensor([wall, float(iters), t_setup, t_loop], device=dev, dtype=torch.float64)
