@@ -340,6 +340,159 @@ __global__ void __launch_bounds__(LBX* LBY) loss_kernel(
     }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Tracker hot path (depth + edge terms, masked, d loss / d(D, alpha) out): the same arithmetic as loss_kernel<0> with
+// the index work stripped (the general kernel issues ~430 instructions per pixel, more than half of them integer /
+// address / control for its flat loops, 64-bit indexing and run-time modes).  32x8 pixels per block, thread = pixel:
+//   * A's halo-2 window is staged with a 2-D thread map (one load per thread, 0.7 more for the margins);
+//   * E(B) comes from the per-frame cache ``gt_edge`` unless the window holds a masked pixel (d == 0): then B's window is
+//     staged too and E(B) recomputed exactly as loss_kernel does (holes are rare: block-uniform branch);
+//   * K = w_s sgn(E(A) - E(B)) / E(A) * grad(A) on the halo-1 window: one position per thread + 84 margin positions
+//     packed into three warps; 8 LDS at immediate offsets from one base;
+//   * the transposed Sobel is 6 + 6 taps (the middle column of Kx and the middle row of Ky have weight 0).
+__global__ void __launch_bounds__(LBX* LBY) loss_track_kernel(
+    int W, int H, const float* __restrict__ ed, const float* __restrict__ alpha, const float* __restrict__ gt,
+    const float* __restrict__ gt_edge, float w_d, float w_s, float* __restrict__ v_out, float* __restrict__ v_alpha,
+    float* __restrict__ partial, const int* __restrict__ stop) {
+    __shared__ float sA[LH * LW], sB[LH * LW];
+    __shared__ float sKx[(LBY + 2) * (LBX + 2)], sKy[(LBY + 2) * (LBX + 2)];
+    __shared__ float s_red[2][(LBX * LBY) / 32];
+    const int cam = blockIdx.z;
+    if (stop && stop[cam]) return;
+    const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * LBX + tx;
+    const int x0 = blockIdx.x * LBX, y0 = blockIdx.y * LBY;
+    const int cam_off = cam * H * W;
+    const float* d_img = ed + cam_off;
+
+    // ---- stage A (= d) on rows y0-2 .. y0+9, columns x0-2 .. x0+33 (replicate padding)
+    const int xa = min(max(x0 + tx - 2, 0), W - 1), xb = min(x0 + tx + 30, W - 1);      // columns tx and tx + 32
+    const int ya = min(max(y0 + ty - 2, 0), H - 1), yb = min(y0 + ty + 6, H - 1);       // rows ty and ty + 8
+    // (everything this thread will want from global memory later is requested now: one round trip instead of three)
+    const int x = x0 + tx, y = y0 + ty;
+    const bool in_img = x < W && y < H;
+    const int pix_c = min(y, H - 1) * W + min(x, W - 1);
+    const float pre_gt = gt[pix_c], pre_al = alpha[cam_off + pix_c];
+    const int ym1 = y0 + ty - 1, xm1 = x0 + tx - 1;   // the pixel of this thread's K position (ty, tx)
+    const float pre_eb = gt_edge[min(max(ym1, 0), H - 1) * W + min(max(xm1, 0), W - 1)];
+    int hole = 0;
+    {
+        const float d = d_img[ya * W + xa];
+        sA[ty * LW + tx] = d; hole |= (d == 0.f);
+    }
+    if (tx < 4) { const float d = d_img[ya * W + xb]; sA[ty * LW + tx + 32] = d; hole |= (d == 0.f); }
+    if (ty < 4) {
+        const float d = d_img[yb * W + xa];
+        sA[(ty + 8) * LW + tx] = d; hole |= (d == 0.f);
+        if (tx < 4) { const float d2 = d_img[yb * W + xb]; sA[(ty + 8) * LW + tx + 32] = d2; hole |= (d2 == 0.f); }
+    }
+    const bool masked = __syncthreads_or(hole) != 0;
+    if (masked) {   // rare: B = gt where d != 0, else 0 (gs_trainer_total.py:109,127-128)
+        sB[ty * LW + tx] = (sA[ty * LW + tx] == 0.f) ? 0.f : gt[ya * W + xa];
+        if (tx < 4) sB[ty * LW + tx + 32] = (sA[ty * LW + tx + 32] == 0.f) ? 0.f : gt[ya * W + xb];
+        if (ty < 4) {
+            sB[(ty + 8) * LW + tx] = (sA[(ty + 8) * LW + tx] == 0.f) ? 0.f : gt[yb * W + xa];
+            if (tx < 4) sB[(ty + 8) * LW + tx + 32] = (sA[(ty + 8) * LW + tx + 32] == 0.f) ? 0.f : gt[yb * W + xb];
+        }
+        __syncthreads();
+    }
+
+    // ---- K on the halo-1 window: position (r, c) <-> pixel (y0 + r - 1, x0 + c - 1), r < 10, c < 34
+    float sum_s = 0.f;
+    auto edge_term = [&](int r, int c, bool have_eb) {
+        const int y = y0 + r - 1, x = x0 + c - 1;
+        float kx = 0.f, ky = 0.f;
+        if ((unsigned)y < (unsigned)H && (unsigned)x < (unsigned)W) {
+            const float* a = sA + r * LW + c;   // top-left of the 3x3 window
+            const float a00 = a[0], a01 = a[1], a02 = a[2], a10 = a[LW], a12 = a[LW + 2];
+            const float a20 = a[2 * LW], a21 = a[2 * LW + 1], a22 = a[2 * LW + 2];
+            const float gxA = ((a02 - a00) + 2.f * (a12 - a10) + (a22 - a20)) * 0.125f;
+            const float gyA = ((a20 - a00) + 2.f * (a21 - a01) + (a22 - a02)) * 0.125f;
+            const float sq = fmaf(gxA, gxA, fmaf(gyA, gyA, 1e-6f));
+            const float rs = rsqrtf(sq);
+            float EB;
+            if (!masked) {
+                EB = have_eb ? pre_eb : gt_edge[y * W + x];
+            } else {
+                const float* bq = sB + r * LW + c;
+                const float b00 = bq[0], b01 = bq[1], b02 = bq[2], b10 = bq[LW], b12 = bq[LW + 2];
+                const float b20 = bq[2 * LW], b21 = bq[2 * LW + 1], b22 = bq[2 * LW + 2];
+                const float gxB = ((b02 - b00) + 2.f * (b12 - b10) + (b22 - b20)) * 0.125f;
+                const float gyB = ((b20 - b00) + 2.f * (b21 - b01) + (b22 - b02)) * 0.125f;
+                EB = sqrtf(gxB * gxB + gyB * gyB + 1e-6f);
+            }
+            const float diff = sq * rs - EB;                                    // E(A) - E(B)
+            const float k = (diff == 0.f) ? 0.f : copysignf(w_s * rs, diff);     // w_s sgn(E(A) - E(B)) / E(A)
+            kx = k * gxA; ky = k * gyA;
+            if ((unsigned)(r - 1) < (unsigned)LBY && (unsigned)(c - 1) < (unsigned)LBX) sum_s += fabsf(diff);
+        }
+        sKx[r * (LBX + 2) + c] = kx; sKy[r * (LBX + 2) + c] = ky;
+    };
+    edge_term(ty, tx, true);
+    if (tid < 84) {   // margins: rows 8, 9 (68 positions) and columns 32, 33 of rows 0..7 (16 positions)
+        if (tid < 68) edge_term(8 + (tid >= 34 ? 1 : 0), tid >= 34 ? tid - 34 : tid, false);
+        else edge_term((tid - 68) >> 1, 32 + ((tid - 68) & 1), false);
+    }
+    __syncthreads();
+
+    // ---- own pixel: L1 term + transposed Sobel of K, chained through ED = D / max(alpha, 1e-10)
+    float sum_d = 0.f;
+    if (in_img) {
+        const float a = sA[(ty + 2) * LW + tx + 2];
+        const float g_own = masked ? sB[(ty + 2) * LW + tx + 2] : pre_gt;
+        sum_d = fabsf(a - g_own);
+        float v = w_d * sgn(a - g_own);
+        const float* kxp = sKx + ty * (LBX + 2) + tx;   // top-left of the 3x3 window of K around (ty + 1, tx + 1)
+        const float* kyp = sKy + ty * (LBX + 2) + tx;
+        constexpr int KW = LBX + 2;
+        if (x >= 1 && x <= W - 2 && y >= 1 && y <= H - 2) {
+            float vx = kxp[KW] - kxp[KW + 2];
+            vx = fmaf(2.f, vx, kxp[0] - kxp[2]) + (kxp[2 * KW] - kxp[2 * KW + 2]);
+            float vy = kyp[1] - kyp[2 * KW + 1];
+            vy = fmaf(2.f, vy, kyp[0] - kyp[2 * KW]) + (kyp[2] - kyp[2 * KW + 2]);
+            v = fmaf(0.125f, vx + vy, v);
+        } else {
+            // border: with replicate padding A(outside) = A(clamped), so this pixel also collects what the plain stencil
+            // sends to its mirror positions one step outside the image (K is 0 out there: out-of-window reads are 0)
+            auto kat = [&](const float* k, int rr, int cc) {
+                return ((unsigned)rr < (unsigned)(LBY + 2) && (unsigned)cc < (unsigned)KW) ? k[rr * KW + cc] : 0.f;
+            };
+            float acc = 0.f;
+            for (int sy = -1; sy <= 1; ++sy) {
+                if (!(sy == 0 || (sy < 0 && y == 0) || (sy > 0 && y == H - 1))) continue;
+                for (int sx = -1; sx <= 1; ++sx) {
+                    if (!(sx == 0 || (sx < 0 && x == 0) || (sx > 0 && x == W - 1))) continue;
+                    const int r = ty + 1 + sy, c = tx + 1 + sx;   // K-window coordinates of the (mirror) position
+                    float vx = kat(sKx, r, c - 1) - kat(sKx, r, c + 1);
+                    vx = 2.f * vx + (kat(sKx, r - 1, c - 1) - kat(sKx, r - 1, c + 1)) + (kat(sKx, r + 1, c - 1) - kat(sKx, r + 1, c + 1));
+                    float vy = kat(sKy, r - 1, c) - kat(sKy, r + 1, c);
+                    vy = 2.f * vy + (kat(sKy, r - 1, c - 1) - kat(sKy, r + 1, c - 1)) + (kat(sKy, r - 1, c + 1) - kat(sKy, r + 1, c + 1));
+                    acc += vx + vy;
+                }
+            }
+            v = fmaf(0.125f, acc, v);
+        }
+        if (a == 0.f) v = 0.f;
+        const int pix = cam_off + y * W + x;
+        const float al = pre_al;
+        const float vq = __fdividef(v, fmaxf(al, 1e-10f));
+        v_out[pix] = vq;
+        v_alpha[pix] = (al >= 1e-10f) ? -vq * a : 0.f;
+    }
+    // ---- block partial sums (fixed order); slot 2 (cosine sum of the normal term) is 0
+    const float sd = warp_sum(sum_d), ss = warp_sum(sum_s);
+    if (tx == 0) { s_red[0][ty] = sd; s_red[1][ty] = ss; }
+    __syncthreads();
+    if (tid < 3) {
+        float t = 0.f;
+        if (tid < 2) {
+#pragma unroll
+            for (int w = 0; w < (LBX * LBY) / 32; ++w) t += s_red[tid][w];
+        }
+        const int blk = (cam * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        partial[blk * 3 + tid] = t;
+    }
+}
+
 void loss_grid(int W, int H, int* gx, int* gy) {
     *gx = (W + LBX - 1) / LBX;
     *gy = (H + LBY - 1) / LBY;
@@ -356,6 +509,11 @@ void launch_loss(int C, int W, int H, const float* ed, const float* alpha, const
     loss_grid(W, H, &gx, &gy);
     dim3 grid(gx, gy, C), block(LBX, LBY);
     if (lambda_n == 0.f) normal_mode = 0;
+    if (normal_mode == 0 && gt_edge && apply_mask && mode == 1 && gt_cam_stride == 0 && LBX == 32 &&
+        (long long)C * W * H < (1ll << 31)) {   // the tracker's configuration: the lean kernel
+        loss_track_kernel<<<grid, block, 0, st>>>(W, H, ed, alpha, gt, gt_edge, w_d, w_s, v_out, v_alpha, partial, stop);
+        return;
+    }
     if (normal_mode == 2) {
         normal_rowsum_kernel<<<dim3(H, C), 256, 0, st>>>(W, H, ed, gt, gt_cam_stride, apply_mask, Ks, normal_rows, stop);
         loss_kernel<2><<<grid, block, 0, st>>>(C, W, H, ed, alpha, gt, gt_cam_stride, apply_mask, w_d, w_s,

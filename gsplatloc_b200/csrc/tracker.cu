@@ -550,6 +550,15 @@ int gsb_tracker_debug_limit_bins(gsb_tracker* t, int tile_cap) {
 
 void* gsb_tracker_stream(gsb_tracker* t) { return t ? (void*)t->stream : nullptr; }
 
+int gsb_tracker_debug_loss_grads(gsb_tracker* t, float* v_depth, float* v_alpha) {
+    if (!t) return fail(GSB_ERR_ARG, "gsb_tracker_debug_loss_grads: null", cudaSuccess);
+    const size_t bytes = sizeof(float) * (size_t)t->C * t->W * t->H;
+    if (v_depth) TCK(cudaMemcpyAsync(v_depth, t->v_depth, bytes, cudaMemcpyDeviceToDevice, t->stream), "debug copy");
+    if (v_alpha) TCK(cudaMemcpyAsync(v_alpha, t->v_alpha, bytes, cudaMemcpyDeviceToDevice, t->stream), "debug copy");
+    TCK(cudaStreamSynchronize(t->stream), "debug copy sync");
+    return GSB_OK;
+}
+
 int gsb_tracker_debug_copy(gsb_tracker* t, int32_t* flatten_ids, int32_t* offsets, float* records) {
     if (!t) return fail(GSB_ERR_ARG, "gsb_tracker_debug_copy: null", cudaSuccess);
     cudaStream_t st = t->stream;

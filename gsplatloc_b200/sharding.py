@@ -91,7 +91,7 @@ class SequenceResult:
 def chained_pose(st: dict, use_best: bool = True):
     """Pose a finished loop hands to the next one: the pose at the best-loss step when early stopping recorded one
     (``update_pose``: "update with best pose after a train loop", model.py:41-48), else the last pose."""
-    if use_best and int(st.get("best_iter", -1)) >= 0:
+    if use_best and int(st.get("best_iter", -1)) >= 0 and "best_q" in st and "best_t" in st:
         return st["best_q"], st["best_t"]
     return st["q"], st["t"]
 

@@ -209,6 +209,14 @@ class PoseTracker:
         """Test aid: cap the per-tile bins so that the next ``run`` overflows (``RuntimeError``, code 3)."""
         _lib.check(self._L.gsb_tracker_debug_limit_bins(self._h, int(tile_cap)), "tracker_debug_limit_bins")
 
+    def debug_loss_grads(self):
+        """d loss / d D and d loss / d alpha [C,H,W] of the last iteration (copies), for parity tests."""
+        vd = torch.empty((self.C, self.H, self.W), dtype=torch.float32, device=self.device)
+        va = torch.empty_like(vd)
+        self._order_after_producer(vd)
+        _lib.check(self._L.gsb_tracker_debug_loss_grads(self._h, vd.data_ptr(), va.data_ptr()), "tracker_debug_loss_grads")
+        return vd, va
+
     def debug_tensors(self):
         """Sorted flatten_ids [M], tile offsets [C*T+1] and projected records [C*N,8] of the last forward
         (copies), for parity tests."""

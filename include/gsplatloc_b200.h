@@ -183,6 +183,10 @@ void* gsb_tracker_stream(gsb_tracker* t);
  * The loop keeps one fixed-capacity bin per (camera, tile); this call compacts them into gsplat's layout
  * (isect_offsets / flatten_ids of IDX:14360-14377). */
 int gsb_tracker_debug_copy(gsb_tracker* t, int32_t* flatten_ids, int32_t* offsets, float* records);
+/* d loss / d D and d loss / d alpha of the last iteration [C,H,W] each (what the loss kernel hands to the raster
+ * backward: the adjoint of compute_depth_loss + compute_silhouette_loss, loss.py:10-59, chained through the "ED"
+ * quotient), into caller-allocated DEVICE buffers (either may be NULL); parity-test aid */
+int gsb_tracker_debug_loss_grads(gsb_tracker* t, float* v_depth, float* v_alpha);
 /* test aid for the overflow path: shrink the per-tile bin capacity below what the sizing pass chose, so that the next
  * gsb_tracker_run fills a bin, raises the flag and returns GSB_ERR_OVERFLOW (the bins are re-sized by the next
  * gsb_tracker_set_poses + run). */
