@@ -6,7 +6,8 @@ it is missing (no CPU / PyTorch fallback exists).
 """
 from . import ops
 from .rendering import rasterization
+from .datatypes import AlignData, TensorWrapper
 from .tracker import PoseTracker, TrackerConfig
 
-__all__ = ["rasterization", "ops", "PoseTracker", "TrackerConfig"]
+__all__ = ["rasterization", "ops", "PoseTracker", "TrackerConfig", "AlignData", "TensorWrapper"]
 __version__ = "0.1.0"

@@ -145,10 +145,12 @@ class DepthSequence:
         return len(self._depth_paths)
 
     _divide_in = np.float32          # TUM divides in float32 (dataset.py:204-213), Replica in float64 (:116-124)
+    _crops_depth = True              # only TUM._get_depth crops the image (dataset.py:215-218); Replica's never does,
+                                     # although BaseDataset shrinks h, w, cx, cy for both (:30-35)
 
     def depth(self, index: int) -> np.ndarray:
         d = read_depth_png(self._depth_paths[index]).astype(self._divide_in)
-        if self.crop_edge > 0:
+        if self.crop_edge > 0 and self._crops_depth:
             d = d[self.crop_edge:-self.crop_edge, self.crop_edge:-self.crop_edge]
         return (d / self.scale).astype(np.float32)   # float32 is what to_tensor makes of it before the loop
 
@@ -172,6 +174,7 @@ class Replica(DepthSequence):
     """dataset.py:78-161: ``<folder>/<name>/results/{frame*.jpg, depth*.png}`` in natural order, ``traj.txt`` with one
     row-major 4x4 c2w per line, camera file shared by all scenes."""
     _divide_in = np.float64
+    _crops_depth = False
 
     def __init__(self, name: str = "room0", *, input_folder="datasets/Replica", cfg_file=None):
         root = Path(input_folder)

@@ -146,6 +146,13 @@ def test_replica_reader_on_a_small_tree(tmp_path):
         d, K, c2w = seq[i]
         assert np.array_equal(d, (depths[i].astype(np.float64) / 6553.5).astype(np.float32))
         np.testing.assert_allclose(c2w, poses[i], rtol=1e-15)
+    # crop_edge on Replica: BaseDataset shrinks h, w, cx, cy (dataset.py:30-35) but Replica._get_depth never crops the
+    # image (:116-124; only TUM's does, :215-218) -- the reader reproduces exactly that
+    (root / "cam_crop.json").write_text(json.dumps(
+        {"camera": {"w": 12, "h": 8, "fx": 6.0, "fy": 6.0, "cx": 5.5, "cy": 3.5, "scale": 6553.5, "crop_edge": 2}}))
+    crop = ds.Replica("room0", input_folder=root, cfg_file=root / "cam_crop.json")
+    assert crop.cfg["w"] == 8 and crop.cfg["h"] == 4 and crop.K[0, 2] == 3.5 and crop.K[1, 2] == 1.5
+    assert crop.depth(0).shape == (8, 12) and np.array_equal(crop.depth(0), seq.depth(0))
     (res / "frame11.jpg").write_bytes(b"")
     with pytest.raises(ValueError, match="do not match"):
         ds.Replica("room0", input_folder=root)

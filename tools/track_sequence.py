@@ -46,6 +46,12 @@ def main():
                          "(gs_trainer_total.py:49-63), frames round-robin over ranks.  last / cv: odometry -- the map is "
                          "placed at the TRACKED pose of the previous loop and the loop starts there (last) or at the "
                          "constant-velocity prediction (cv: model.py:41-77); each rank chains a contiguous block")
+    ap.add_argument("--dump-records", default=None, help="rank 0 writes the per-frame result rows (sharding.RECORD_FIELDS) here (.npy)")
+    ap.add_argument("--replay", default=None,
+                    help="comma-separated frame ids: after the walk, rank 0 tracks these frames again and writes their inputs "
+                         "(map, observation, poses) and per-iteration history to --replay-out (.npz) for tools/replay_oracle.py")
+    ap.add_argument("--replay-out", default="gpurun_out/replay_frames.npz")
+    ap.add_argument("--replay-only", action="store_true", help="skip the walk: ray cast and track the --replay frames only")
     args = ap.parse_args()
 
     import torch.distributed as dist
@@ -65,6 +71,8 @@ def main():
     chained = args.chain != "off"
     mine = (list(sharding.hypotheses_of_rank(args.frames, rank, world)) if chained
             else sharding.frames_of_rank(args.frames, rank, world))
+    if args.replay and args.replay_only:
+        mine = [int(x) for x in args.replay.split(",")] if rank == 0 else []
     # ---- the "dataset": every rank ray casts the whole walk (cheap, deterministic) and keeps its own frames
     rng = np.random.default_rng(args.seed)
     scene = syn.make_scene(rng)
@@ -168,6 +176,27 @@ def main():
             "iters_min_max": [int(records[:, 2].min()), int(records[:, 2].max())],
             "ATE_rmse_m": err["ATE_rmse_m"], "AAE_rmse_deg": err["AAE_rmse_deg"],
             "ATE_rmse_m_at_best_loss": best["ATE_rmse_m"], "AAE_rmse_deg_at_best_loss": best["AAE_rmse_deg"]}), flush=True)
+        if args.dump_records:
+            np.save(args.dump_records, records)
+        if args.replay:
+            out = {}
+            for f in [int(x) for x in args.replay.split(",")]:
+                fr = frames[f]
+                m = setup(fr, fr["c2w_tar"])
+                obs = observation(fr)
+                trk.set_map(*m)
+                trk.set_observation(obs, K32)
+                trk.set_poses(fr["c2w_tar"], fr["c2w_src"])
+                trk.run(None, poll_every=25, use_graph=True)
+                st = trk.states()[0]
+                out.update({f"f{f}_means": m[0].cpu().numpy(), f"f{f}_scales": m[2].cpu().numpy(),
+                            f"f{f}_obs": obs.cpu().numpy(), f"f{f}_c2w_init": fr["c2w_tar"], f"f{f}_c2w_gt": fr["c2w_src"],
+                            f"f{f}_history": trk.history(0), f"f{f}_best": np.array([st["best_iter"], st["best_eT"], st["best_eR"],
+                                                                                    st["best_loss"], st["iter"]], dtype=np.float64)})
+            out["K"] = K32
+            out["frames"] = np.array([int(x) for x in args.replay.split(",")])
+            out["cfg"] = np.array([args.max_steps, args.patience, 100], dtype=np.int64)
+            np.savez_compressed(args.replay_out, **out)
     trk.close()
     if world > 1:
         dist.destroy_process_group()
