@@ -35,6 +35,7 @@ WORKLOADS = {
     # name: (camera dict name, lattice stride, translation cm, rotation deg)
     "replica200k": ("REPLICA", 2, 2.0, 1.0),      # BASELINE.json configs[1]  (S2)
     "replica50k": ("REPLICA", 4, 2.0, 1.0),       # configs[0]               (S1)
+    "replica816k": ("REPLICA", 1, 2.0, 1.0),      # every pixel back-projected, as RGBDImage does (src/data/Image.py:29)
     "tum77k": ("TUM", 2, 6.0, 3.0),               # configs[2]               (S3)
     "hd500k": ("HD", 2, 2.0, 1.0),                # towards configs[4]       (S5)
     "hd2m": ("HD", 1, 2.0, 1.0),                  # configs[4]: 1920x1080, 2.07 M Gaussians (S5)
@@ -47,6 +48,27 @@ def peaks():
         d = json.load(open(p))
         return float(d["hbm_gbs"]), "measured"
     return 6650.0, "fallback"
+
+
+def probe_gsplat() -> str:
+    """BASELINE.md §1 / SURVEY.md §8(d): the '>= 10x gsplat CUDA' target needs gsplat's own CUDA path on this box.
+    One guarded import, result recorded in the bench line."""
+    try:
+        import gsplat  # noqa: F401
+        from gsplat import rasterization  # noqa: F401
+        return f"importable: gsplat {getattr(gsplat, '__version__', '?')} (not timed here)"
+    except Exception as e:   # ModuleNotFoundError on this image: the submodule is empty and there is no wheel
+        return f"unavailable: {type(e).__name__}: {e}"
+
+
+def kernel_counters(workload: str) -> dict:
+    """profiles/kernel_counters.json (tools/ncu_counters.py from the committed ncu capture): DRAM bytes and warp
+    instructions per launch of every kernel of the iteration."""
+    p = os.path.join(ROOT, "profiles", "kernel_counters.json")
+    try:
+        return json.load(open(p)).get(workload, {})
+    except Exception:
+        return {}
 
 
 class ClockSampler:
@@ -146,26 +168,33 @@ def run_native(args, rank, world, local_rank):
     dev = torch.device("cuda", local_rank)
     K, W_, iters = args.steps, args.warmup, args.iters
     n_pool = args.pool
-    frames = make_frames(args.workload, n_pool, seed0=42 + 1000 * rank)     # rank r owns its own frames
-    Cn = max(1, args.cameras)                                                # pose hypotheses per frame (configs[3])
+    split_h = args.split == "hypotheses"
+    # --split frames (default): rank r owns its own frames.  --split hypotheses (BASELINE.json configs[3]): every rank
+    # holds the SAME frames and a contiguous block of the pose hypotheses of each (sharding.hypotheses_of_rank)
+    frames = make_frames(args.workload, n_pool, seed0=42 + (0 if split_h else 1000 * rank))
+    Ctot = max(1, args.cameras)                                              # pose hypotheses per frame (configs[3])
+    my_h = list(sharding.hypotheses_of_rank(Ctot, rank, world)) if split_h else list(range(Ctot))
+    Cn = len(my_h)
+    if Cn == 0:
+        raise RuntimeError(f"--split hypotheses: {Ctot} hypotheses cannot be split over {world} ranks")
     cfg = TrackerConfig(max_steps=args.max_steps, early_stop=False,          # fixed 100 steps for timing (S2)
                         depth_lambda=args.depth_lambda, normal_lambda=args.normal_lambda)
 
     def start_poses(fp, seed):
         """configs[3] (S4): the start pose perturbed by N(0, (1 cm)^2), N(0, (0.5 deg)^2) per hypothesis."""
-        if Cn == 1:
+        if Ctot == 1:
             return fp.tar_c2w
         from gsplatloc_b200 import synthetic as syn
         rng = np.random.default_rng(seed)
         out = []
-        for c in range(Cn):
+        for c in range(Ctot):
             p = fp.tar_c2w.copy()
             if c:
                 p[:3, 3] += rng.normal(0, 0.01, 3).astype(np.float32)
                 r = np.deg2rad(rng.normal(0, 0.5, 3))
                 p[:3, :3] = (p[:3, :3] @ syn._rot_xyz(*r)).astype(np.float32)
             out.append(p)
-        return np.stack(out)
+        return np.stack(out)[my_h]
     host = []
     trackers = []
     stream = torch.cuda.Stream(dev)          # every tracker launches here; the timing events are recorded here
@@ -223,7 +252,10 @@ def run_native(args, rank, world, local_rank):
     ms = e0.elapsed_time(e1)
     clocks = sampler.stop(wall0, wall1) if sampler else None
     launches = sum(t.counters()["total_launches"] for t in trackers) - launches0
-    records = [sharding.state_to_record(i * world + rank, rank, t.states()[0]) for i, t in enumerate(trackers)]
+    if split_h:   # one row per hypothesis of the first frame: unit = global hypothesis index
+        records = [sharding.state_to_record(my_h[c], rank, st) for c, st in enumerate(trackers[0].states())]
+    else:
+        records = [sharding.state_to_record(i * world + rank, rank, t.states()[0]) for i, t in enumerate(trackers)]
     M = int(np.mean([t.counters()["n_isects"] for t in trackers]))
 
     # ---------------------------------------------------------------- end-to-end leg (host buffers)
@@ -259,7 +291,8 @@ def run_native(args, rank, world, local_rank):
     records = sharding.gather_records(records, dev)        # the path's one collective: final gather of pose errors
     if rank != 0:
         return
-    total_iters = K * iters * world * Cn     # every hypothesis of every frame advances one iteration per launch set
+    # every hypothesis of every frame advances one iteration per launch set
+    total_iters = K * iters * (Ctot if split_h else world * Cn)
     value = total_iters / (ms * 1e-3)
     e2e_v = total_iters / (ms_e2e * 1e-3)
     peak, peak_src = peaks()
@@ -273,13 +306,16 @@ def run_native(args, rank, world, local_rank):
     iter_bytes = sum(algorithmic_bytes(k, Cn, N, M, P * Cn, T * Cn) for k in stage_ms)
     out = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W_,
-        "ms_per_step": round(ms / K, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": round(ms / K, 4), "higher_is_better": True, "scaling": "strong" if split_h else "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {fp0.W}x{fp0.H}, N={N} Gaussians, M={M} tile intersections, "
                                f"{iters}-iteration pose optimisation per step (BASELINE.json configs[1])",
-                   "iters_per_step": iters, "hypotheses": Cn, "depth_lambda": args.depth_lambda,
+                   "iters_per_step": iters, "hypotheses": Ctot, "hypotheses_per_rank": Cn, "split": args.split,
+                   "frame_iters_per_s": round(value / Ctot, 2), "depth_lambda": args.depth_lambda,
                    "normal_lambda": args.normal_lambda, "gaussians": N, "isects": M, "pixels": P, "tiles": T,
-                   "frames_per_rank": n_pool, "sharding": "independent frames per rank, final all_gather of pose errors",
+                   "frames_per_rank": n_pool,
+                   "sharding": ("one frame, its pose hypotheses in contiguous blocks over the ranks, final all_gather + argmin"
+                                if split_h else "independent frames per rank, final all_gather of pose errors"),
                    "l2": f"inputs larger than L2: {n_pool} frames x ~{round((44*N + 24*P + 12*M + 40*N) / 1e6)} MB of "
                          "buffers cycled between steps; iterations inside a step reuse L2 as the real loop does",
                    "timing": "CUDA events on the launching stream, barrier+synchronize both sides, max over ranks"},
@@ -296,15 +332,108 @@ def run_native(args, rank, world, local_rank):
                      "stages": stages},
         "pose_errors": sharding.trajectory_errors(records),
     }
-    traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(traffic_file):
-        try:
-            out["roofline"]["traffic"] = json.load(open(traffic_file)).get(args.workload, {}).get(dom)
-        except Exception:
-            pass
+    if split_h:
+        out["best_hypothesis"] = {"index": sharding.best_hypothesis(records), "of": int(records.shape[0])}
+    kc = kernel_counters(args.workload) if Cn == 1 else {}
+    if dom in kc:
+        out["roofline"]["traffic"] = kc[dom]["dram_bytes"]
+        out["roofline"]["traffic_source"] = f"profiles/kernel_counters.json <- {kc.get('source')}"
+    # the roofline that binds the rasterisers is the SM's instruction issue rate, not HBM: warp
+    # instructions per launch (ncu, same capture) / live kernel time / (SMs x 4 schedulers x SM clock)
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    issue_peak = 148 * 4 * sm_mhz * 1e6
+    out["roofline"]["issue"] = {
+        "unit": "warp instructions/s", "peak": issue_peak, "sm_mhz": sm_mhz,
+        "kernels": {k: {"warp_inst": kc[k]["warp_inst"], "achieved": round(kc[k]["warp_inst"] / (stage_ms[k] * 1e-3), 1),
+                        "frac": round(kc[k]["warp_inst"] / (stage_ms[k] * 1e-3) / issue_peak, 4)}
+                    for k in stage_ms if k in kc and stage_ms[k] > 0}}
+    out["gsplat_cuda"] = probe_gsplat()
     if not args.no_cpu_baseline and world == 1:
         out["cpu_baseline"] = cpu_oracle(args.workload, frames[0], n_timed=args.cpu_iters, warm=1)
     print(json.dumps(out), flush=True)
+
+
+def run_dropin(args):
+    """--api rasterization: the zero-code-change route of INTEGRATION.md §1 -- GsplatLoc's own loop shape with
+    ``from gsplatloc_b200 import rasterization`` in place of gsplat's: CameraOptModule-style quaternion + translation
+    parameters in torch, ``rasterization(render_mode="RGB+ED", sh_degree=1)`` exactly as GSModel.forward calls it
+    (model.py:195-213), mask + depth + silhouette loss (gs_trainer_total.py:104-152), ``backward()``, two torch Adam
+    steps and two ExponentialLR steps per iteration.  One GPU, frame resident; reported beside the tracker's number."""
+    from gsplatloc_b200 import _lib, rasterization
+    from gsplatloc_b200.losses import compute_depth_loss, compute_silhouette_loss
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: gsplatloc_b200 has no CPU path")
+    _lib.lib()
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    from gsplatloc_b200 import PoseTracker
+    fp = make_frames(args.workload, 1, seed0=42)[0]
+    N = fp.tar_points.shape[0]
+    means = torch.tensor(fp.tar_points, device=dev)
+    quats = torch.tensor([[1.0, 0, 0, 0]], device=dev).repeat(N, 1)
+    scales = torch.tensor(fp.scales, device=dev)
+    opac_logit = torch.full((N,), 1.0, device=dev)                        # GsConfig.init_opa (model.py:121)
+    colors = torch.zeros((N, 4, 3), device=dev)                           # sh0 + shN, sh_degree 1 (model.py:150-160)
+    gt = rendered_observation(PoseTracker, fp, dev)[None, :, :, None]     # [1, H, W, 1]
+    Ks = torch.tensor(fp.K, device=dev)[None]
+    c2w0 = torch.tensor(fp.tar_c2w, device=dev)
+
+    def rotmat(q):   # kornia quaternion (wxyz) -> rotation matrix, normalised (transform.py:50-66)
+        w, x, y, z = (q / q.norm())
+        return torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y),
+                            2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x),
+                            2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]).reshape(3, 3)
+
+    def one_frame(n_iters):
+        from gsplatloc_b200.motion import rotation_matrix_to_quaternion
+        q = torch.tensor(rotation_matrix_to_quaternion(fp.tar_c2w[:3, :3]), device=dev, dtype=torch.float32).requires_grad_(True)
+        t = c2w0[:3, 3].clone().requires_grad_(True)
+        opts = [torch.optim.Adam([q], lr=5e-4, weight_decay=1e-3), torch.optim.Adam([t], lr=1e-3, weight_decay=1e-3)]
+        gamma = 0.2 ** (1.0 / args.max_steps)
+        scheds = [torch.optim.lr_scheduler.ExponentialLR(o, gamma=gamma) for o in opts]
+        bottom = torch.tensor([[0.0, 0, 0, 1]], device=dev)
+        last = None
+        for _ in range(n_iters):
+            c2w = torch.cat([torch.cat([rotmat(q), t[:, None]], 1), bottom], 0)
+            renders, alphas, info = rasterization(means=means, quats=quats, scales=scales, opacities=torch.sigmoid(opac_logit),
+                                                  colors=colors, sh_degree=1, viewmats=torch.linalg.inv(c2w)[None], Ks=Ks,
+                                                  width=fp.W, height=fp.H, packed=False, absgrad=False, sparse_grad=False,
+                                                  far_plane=1e10, near_plane=1e-2, render_mode="RGB+ED",
+                                                  rasterize_mode="classic")
+            depths = renders[..., 3:4]
+            mask = (depths != 0).float()
+            dl = compute_depth_loss(depths * mask, gt * mask, loss_type="l1")
+            sl = compute_silhouette_loss(depths * mask, gt * mask, loss_type="l1")
+            total = dl * args.depth_lambda + sl * (1 - args.depth_lambda)
+            total.backward()
+            for o in opts:
+                o.step(); o.zero_grad(set_to_none=True)
+            for sc in scheds:
+                sc.step()
+            last = total.detach()
+        return float(last)   # D2H of the loss: the one host read per frame
+
+    K, W_, iters = args.steps, args.warmup, args.iters
+    for _ in range(max(W_, 1)):
+        one_frame(min(iters, 10))
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        loss = one_frame(iters)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1)
+    value = K * iters / (ms * 1e-3)
+    print(json.dumps({"metric": METRIC, "api": "rasterization", "value": round(value, 2), "unit": UNIT, "n_gpus": 1, "steps": K,
+                      "warmup": W_, "ms_per_step": round(ms / K, 4), "higher_is_better": True, "scaling": "weak",
+                      "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                      "config": {"workload": f"{args.workload}: {fp.W}x{fp.H}, N={N} Gaussians; drop-in route: "
+                                             "gsplatloc_b200.rasterization(RGB+ED, sh_degree 1) + torch autograd + torch Adam, "
+                                             f"{iters} iterations per step", "iters_per_step": iters, "final_loss": loss},
+                      "note": "every iteration pays gsplat's own API contract: exact-size isect tensors (one host sync for "
+                              "n_isects, as in gsplat), per-call allocations, the general backward (per-Gaussian gradients by "
+                              "atomics) and ~40 torch launches; the device-resident tracker is the measured headline"}), flush=True)
 
 
 def cpu_oracle(workload, fp, n_timed=2, warm=1):
@@ -367,6 +496,12 @@ def main():
     ap.add_argument("--max-steps", type=int, default=2000, help="LR schedule horizon (GsplatLoc_eval.py --num-iters)")
     ap.add_argument("--pool", type=int, default=4, help="distinct frames cycled per rank")
     ap.add_argument("--cameras", type=int, default=1, help="pose hypotheses per frame (BASELINE.json configs[3]: 64)")
+    ap.add_argument("--split", default="frames", choices=["frames", "hypotheses"],
+                    help="what the ranks shard: independent frames (weak scaling) or the pose hypotheses of one frame (strong)")
+    ap.add_argument("--api", default="tracker", choices=["tracker", "rasterization"],
+                    help="tracker: the device-resident loop (headline). rasterization: the drop-in route, one "
+                         "gsplatloc_b200.rasterization() + torch autograd + torch Adam per iteration, as model.py:195-213 "
+                         "and gs_trainer_total.py:95-152 drive gsplat")
     ap.add_argument("--depth-lambda", type=float, default=0.8)
     ap.add_argument("--normal-lambda", type=float, default=0.0)
     ap.add_argument("--cpu-iters", type=int, default=6, help="timed CPU-oracle iterations (~1.6 s each on 16 cores)")
@@ -378,6 +513,10 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         run_reference(args, rank, world)
+        return
+    if args.api == "rasterization":
+        if rank == 0:
+            run_dropin(args)
         return
     if world > 1:
         import torch.distributed as dist

@@ -77,6 +77,10 @@ _SIGS = {
     "gsb_tracker_debug_copy": (c_i, [c_p, c_p, c_p, c_p]),
     "gsb_tracker_debug_limit_bins": (c_i, [c_p, c_i]),
     "gsb_tracker_debug_loss_grads": (c_i, [c_p, c_p, c_p]),
+    "gsb_tracker_set_stripe": (c_i, [c_p, c_i, c_i]),
+    "gsb_tracker_stripe_segment": (c_i, [c_p, c_i]),
+    "gsb_tracker_stripe_buffers": (c_i, [c_p, c_p, c_p, c_p, c_p]),
+    "gsb_tracker_stripe_finish": (c_i, [c_p, c_p, c_p]),
     "gsb_knn_sq_dists": (c_i, [c_i, c_p, c_i, c_p, C.POINTER(c_i), c_p]),
     "gsb_init_gs_scales": (c_i, [c_i, c_p, c_i, c_f, c_i, c_p, c_p]),
     "gsb_depth_to_points": (c_i, [c_i, c_i, c_p, C.POINTER(c_f), C.POINTER(c_f), c_p, c_p]),

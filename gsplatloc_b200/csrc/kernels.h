@@ -26,7 +26,7 @@ void launch_project_emit(int C, int N, const float* means, const float* quats, c
                          const float* opacities, const float* viewmats, const float* Ks, int W, int H, int tile_w,
                          int tile_h, float eps2d, float near_plane, float far_plane, float radius_clip, float4* rec,
                          int* cursor, uint64_t* keys, int tile_cap, int* n_isects, int* overflow, const int* stop,
-                         cudaStream_t st);
+                         int stripe_rank, int stripe_world, cudaStream_t st);
 
 // ---- isect.cu
 void launch_isect_count(int CN, const float* means2d, const int* radii, int tile_size, int tile_w, int tile_h,
@@ -60,7 +60,7 @@ void launch_compact_bins(int n_bins, const int2* ranges, const int* padded, cons
 void launch_raster_fwd_packed(int C, int W, int H, int tile_w, int tile_h, const float4* rec, const int2* ranges,
                               const int* flatten_ids, float* render_depth,
                               float* render_alphas, int* last_ids, int normalize, const int* stop,
-                              unsigned char* masks_out, cudaStream_t st);
+                              unsigned char* masks_out, int stripe_rank, int stripe_world, cudaStream_t st);
 int launch_raster_fwd_soa(int cdim, int C, int W, int H, int tile_w, int tile_h, const float* means2d,
                           const float* conics, const float* colors, const float* opacities, const float* backgrounds,
                           const int* tile_offsets, int n_isects, const int* flatten_ids, float* render_colors,
@@ -70,7 +70,8 @@ void launch_raster_bwd_lift(int C, int N, int W, int H, int tile_w, int tile_h, 
                             const float* render_alphas, const int* last_ids, const float* v_depth,
                             const float* v_alpha, const float* means, const float* quats, const float* scales,
                             const float* viewmats, const float* Ks, float eps2d, float* partials, const int* stop,
-                            const unsigned char* masks, const int* iso_flag, cudaStream_t st);
+                            const unsigned char* masks, const int* iso_flag, int stripe_rank, int stripe_world,
+                            cudaStream_t st);
 void launch_map_iso(int N, const float* scales, int* flag, cudaStream_t st);
 int launch_raster_bwd_soa(int cdim, int C, int N, int W, int H, int tile_w, int tile_h, const float* means2d,
                           const float* conics, const float* colors, const float* opacities, const float* backgrounds,

@@ -203,7 +203,11 @@ __global__ void __launch_bounds__(256) project_emit_kernel(
     const float* __restrict__ opacities, const float* __restrict__ viewmats, const float* __restrict__ Ks, int W, int H,
     int tile_w, int tile_h, float eps2d, float near_plane, float far_plane, float radius_clip,
     float4* __restrict__ rec, int* __restrict__ cursor, uint64_t* __restrict__ keys, int tile_cap,
-    int* __restrict__ n_isects, int* __restrict__ overflow, const int* __restrict__ stop) {
+    int* __restrict__ n_isects, int* __restrict__ overflow, const int* __restrict__ stop, int stripe_rank,
+    int stripe_mask) {
+    // Tile-striped single frame over several GPUs: every rank projects all Gaussians but bins
+    // only into the tiles it owns, tile & stripe_mask == stripe_rank (stripe_mask = world - 1, world a power of two;
+    // 0 = one GPU: every tile).  The records are written for every Gaussian either way.
     __shared__ int s_incl[8][32];
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     const int c = blockIdx.y;
@@ -240,20 +244,23 @@ __global__ void __launch_bounds__(256) project_emit_kernel(
     if (small) {
         const int leader = __ffs(grp) - 1, cnt = __popc(grp), rank = __popc(grp & ((1u << lane) - 1u));
         const int t00 = y0 * tile_w + x0;
-        const bool hx = bw > 1, hy = bh > 1;
+        const bool o0 = (t00 & stripe_mask) == stripe_rank;
+        const bool hx = bw > 1 && ((t00 + 1) & stripe_mask) == stripe_rank;
+        const bool hy = bh > 1 && ((t00 + tile_w) & stripe_mask) == stripe_rank;
+        const bool hxy = bw > 1 && bh > 1 && ((t00 + tile_w + 1) & stripe_mask) == stripe_rank;
         int b0 = 0, b1 = 0, b2 = 0, b3 = 0;
         if (lane == leader) {
-            b0 = atomicAdd(cur + t00, cnt);
+            if (o0) b0 = atomicAdd(cur + t00, cnt);
             if (hx) b1 = atomicAdd(cur + t00 + 1, cnt);
             if (hy) b2 = atomicAdd(cur + t00 + tile_w, cnt);
-            if (hx && hy) b3 = atomicAdd(cur + t00 + tile_w + 1, cnt);
+            if (hxy) b3 = atomicAdd(cur + t00 + tile_w + 1, cnt);
         }
         b0 = __shfl_sync(grp, b0, leader) + rank; b1 = __shfl_sync(grp, b1, leader) + rank;
         b2 = __shfl_sync(grp, b2, leader) + rank; b3 = __shfl_sync(grp, b3, leader) + rank;
-        if (b0 < tile_cap) kbase[(size_t)t00 * tile_cap + b0] = key; else over = true;
+        if (o0) { if (b0 < tile_cap) kbase[(size_t)t00 * tile_cap + b0] = key; else over = true; }
         if (hx) { if (b1 < tile_cap) kbase[(size_t)(t00 + 1) * tile_cap + b1] = key; else over = true; }
         if (hy) { if (b2 < tile_cap) kbase[(size_t)(t00 + tile_w) * tile_cap + b2] = key; else over = true; }
-        if (hx && hy) { if (b3 < tile_cap) kbase[(size_t)(t00 + tile_w + 1) * tile_cap + b3] = key; else over = true; }
+        if (hxy) { if (b3 < tile_cap) kbase[(size_t)(t00 + tile_w + 1) * tile_cap + b3] = key; else over = true; }
     }
     // larger boxes: (Gaussian, tile) pairs flattened over the warp, 32 per round
     const int mine = (live && !small) ? (int)(bw * bh) : 0;
@@ -283,16 +290,19 @@ __global__ void __launch_bounds__(256) project_emit_kernel(
             const uint32_t shi = __shfl_sync(0xffffffffu, key_hi, src), slo = __shfl_sync(0xffffffffu, (uint32_t)i, src);
             // neighbouring Gaussians with the same big box meet in the same tiles within a round: aggregate again
             int tile = -1 - lane;
+            bool mine_t = false;
             if (w < total) {
                 const uint32_t t = (uint32_t)(w - sexcl);
                 tile = (int)((sy0 + t / sbw) * tile_w + sx0 + t % sbw);
+                mine_t = (tile & stripe_mask) == stripe_rank;
+                if (!mine_t) tile = -1 - lane;   // not this rank's tile: no group, no atomic
             }
             const unsigned g2 = __match_any_sync(0xffffffffu, tile);
             const int ldr = __ffs(g2) - 1;
             int base = 0;
-            if (w < total && lane == ldr) base = atomicAdd(cur + tile, __popc(g2));
+            if (mine_t && lane == ldr) base = atomicAdd(cur + tile, __popc(g2));
             base = __shfl_sync(0xffffffffu, base, ldr);
-            if (w < total) {
+            if (mine_t) {
                 const int pos = base + __popc(g2 & ((1u << lane) - 1u));
                 if (pos < tile_cap) kbase[(size_t)tile * tile_cap + pos] = ((uint64_t)shi << 32) | slo; else over = true;
             }
@@ -305,12 +315,12 @@ void launch_project_emit(int C, int N, const float* means, const float* quats, c
                          const float* opacities, const float* viewmats, const float* Ks, int W, int H, int tile_w,
                          int tile_h, float eps2d, float near_plane, float far_plane, float radius_clip, float4* rec,
                          int* cursor, uint64_t* keys, int tile_cap, int* n_isects, int* overflow, const int* stop,
-                         cudaStream_t st) {
+                         int stripe_rank, int stripe_world, cudaStream_t st) {
     if (N == 0 || C == 0) return;
     dim3 grid((N + 255) / 256, C);
     project_emit_kernel<<<grid, 256, 0, st>>>(C, N, means, quats, scales, opacities, viewmats, Ks, W, H, tile_w, tile_h,
                                               eps2d, near_plane, far_plane, radius_clip, rec, cursor, keys, tile_cap,
-                                              n_isects, overflow, stop);
+                                              n_isects, overflow, stop, stripe_rank, stripe_world - 1);
 }
 
 void launch_project_bin(int C, int N, const float* means, const float* quats, const float* scales,

@@ -3,7 +3,6 @@
 //   raster_bwd_quad_kernel   : tracker path, ED only; per-Gaussian sums never reach HBM: they are lifted through the
 //                              projection Jacobian (A.6) into ONE 12-float d(loss)/d(viewmat[:3,:4]) partial per tile.
 #include <cuda_pipeline_primitives.h>
-#include <stdlib.h>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -83,7 +82,7 @@ struct LiftCtx {
     int W, H, N, cam_index;
     float eps2d;
     int iso;   // every Gaussian has sx == sy == sz: Sigma = s^2 I whatever the quaternion (tracker.cu map_iso_kernel)
-    float inv_fx, inv_fy, limx, limy;   // raster_bwd_quad2_kernel's record-based lift
+    float inv_fx, inv_fy, limx, limy;   // raster_bwd_quad_kernel's record-based lift
 };
 
 // A.6 for one Gaussian: the six patch-summed numbers (v_xy, v_conic, v_depth) -> 12 pose-gradient numbers, accumulated
@@ -287,28 +286,6 @@ __global__ void __launch_bounds__(256, 2) raster_bwd_kernel(
     }
 }
 
-// ------------------------------------------------------------------------------------------------------------------
-// Tracker path: "quad-scan" replay, every warp an independent unit (no __syncthreads until the final reduction).
-//
-// A pixel-per-lane replay (the op-level kernel above) spends a third of its instructions on the 32-lane butterfly that sums six numbers
-// per Gaussian, and evaluates one (pixel, Gaussian) pair per lane per ~120 warp instructions.  Here the warp's 8x4
-// patch is re-mapped: lane L = (column pr = L >> 2, Gaussian pair gq = L & 3) owns the FOUR pixels of column pr and
-// TWO of the eight Gaussians of a step, i.e. 8 pairs per lane per step with all Gaussian data in registers.
-//   * The sequential recurrences of A.5 along the Gaussian axis (T <- T / (1 - alpha), buffer <- buffer + d alpha T)
-//     become a two-element local combine plus a 4-lane scan (2 shuffles) and a 4-lane broadcast per pixel.
-//   * dx is shared by a lane's four pixels, so the five geometric gradients reduce to three moments of v_sigma
-//     (sum v, sum v dy, sum v dy^2) accumulated in registers; only once per step are 12 numbers (2 Gaussians x 6) summed
-//     over the eight columns (12 shuffles for 256 pairs instead of 9 per 32 pairs).
-// The set of (pixel, Gaussian) pairs evaluated, the validity rules and every formula are those of the replay above;
-// only the association order of the per-pixel products / sums differs (1e-7 relative).  Entries are first compacted
-// (patch_mask) into a per-warp ring; a step consumes eight; the summed gradients go to the lift ring as before.
-struct QuadScratch {
-    float4 rec[64][2];   // compacted entries {x, y, a', b'}, {c', opacity, depth, position bits}; a' = -log2(e)/2 * a ...
-    int gid[64];
-    float qsum[64][6];   // lift ring: v_xy[2], v_conic[3], v_depth
-    int qid[64];
-};
-
 #define GSB_NEG_LOG2E -1.4426950408889634f
 #ifndef GSB_BWD_WARPS
 #define GSB_BWD_WARPS 4   // warps (8x4 patches) per block: 8 = one block per tile, 4 = two blocks per tile (finer
@@ -319,226 +296,23 @@ struct QuadScratch {
 #define GSB_BWD_THREADS (32 * GSB_BWD_WARPS)
 #define GSB_BWD_SPLIT (8 / GSB_BWD_WARPS)    // blocks per tile
 
-__global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad_kernel(
-    int C, int N, int W, int H, int tile_w, int tile_h, const float4* __restrict__ rec,
-    const int2* __restrict__ ranges, const int* __restrict__ flatten_ids,
-    const float* __restrict__ render_alphas, const int* __restrict__ last_ids, const float* __restrict__ v_depth,
-    const float* __restrict__ v_alpha_img, const float* __restrict__ means, const float* __restrict__ quats,
-    const float* __restrict__ scales, const float* __restrict__ viewmats, const float* __restrict__ Ks, float eps2d,
-    float* __restrict__ partials, const int* __restrict__ stop, const unsigned char* __restrict__ masks,
-    const int* __restrict__ iso_flag) {
-    __shared__ QuadScratch s_w[GSB_BWD_WARPS];
-    __shared__ float s_pose[12 * GSB_BWD_THREADS];
-    __shared__ LiftCtx s_ctx;
-
-    const int cam = blockIdx.z;
-    if (stop && stop[cam]) return;
-    const int tile_x = blockIdx.x / GSB_BWD_SPLIT, part = blockIdx.x % GSB_BWD_SPLIT;
-    const int tile_id = blockIdx.y * tile_w + tile_x;
-    const int tid = threadIdx.x, lane = tid & 31, lwid = tid >> 5;
-    const int wid = lwid + part * GSB_BWD_WARPS;                  // patch index inside the tile (bit of the patch masks)
-    const int gq = lane & 3, pr = lane >> 2;
-    const int j = tile_x * 16 + (wid & 1) * 8 + pr;               // this lane's pixel column
-    const int i0 = blockIdx.y * 16 + (wid >> 1) * 4;              // first row of the patch
-    const float px = (float)j + 0.5f, py0 = (float)i0 + 0.5f;
-    const float tile_x0 = (float)(tile_x * 16), tile_y0 = (float)(blockIdx.y * 16);
-    const int bin = cam * tile_w * tile_h + tile_id;
-    const int2 range = ranges[bin];   // fixed-capacity bin of this tile (tile_sort_fixed_kernel)
-    const int range_start = range.x, range_end = range.y;
-
-    if (tid == 0) {
-        s_ctx.cam = load_cam(viewmats + cam * 16, Ks + cam * 9);
-        s_ctx.means = means; s_ctx.quats = quats; s_ctx.scales = scales;
-        s_ctx.W = W; s_ctx.H = H; s_ctx.N = N; s_ctx.cam_index = cam; s_ctx.eps2d = eps2d;
-        s_ctx.iso = iso_flag ? *iso_flag : 0;
-    }
-#pragma unroll
-    for (int k = 0; k < 12; ++k) s_pose[k * GSB_BWD_THREADS + tid] = 0.f;
-    __syncthreads();
-
-    // state of the lane's four pixels (replicated in the four lanes of a column)
-    float T[4], buf[4], v_rc[4], v_raT[4];
-    int bin_final[4];
-    int warp_bin_final = -1;
-#pragma unroll
-    for (int r = 0; r < 4; ++r) {
-        const int i = i0 + r;
-        const bool inside = (i < H) && (j < W);
-        const size_t pix = ((size_t)cam * H + min(i, H - 1)) * W + min(j, W - 1);
-        const float Tf = inside ? 1.f - render_alphas[pix] : 1.f;
-        T[r] = Tf; buf[r] = 0.f;
-        v_rc[r] = inside ? v_depth[pix] : 0.f;
-        v_raT[r] = inside ? Tf * v_alpha_img[pix] : 0.f;
-        bin_final[r] = inside ? last_ids[pix] : -1;
-        warp_bin_final = max(warp_bin_final, bin_final[r]);
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) warp_bin_final = max(warp_bin_final, __shfl_xor_sync(0xffffffffu, warp_bin_final, o));
-
-    QuadScratch& ws = s_w[lwid];
-    float* const pose_col = s_pose + tid;
-    int r_head = 0, r_tail = 0;   // compaction ring (uniform)
-    int q_head = 0, q_tail = 0;   // lift ring (uniform)
-    const unsigned lt_mask = (1u << lane) - 1u;
-    const bool up16 = lane & 16, up8 = lane & 8;
-
-    const int first = min(range_end - 1, warp_bin_final);
-    int top = first;
-    bool more = top >= range_start;
-    // (patch mask, Gaussian id) of the chunk about to be gathered are fetched one chunk ahead, so that the dependent
-    // record loads of a chunk are the only global-memory round trip left on the warp's critical path
-    unsigned nxt_m = 0u;
-    int nxt_g = 0;
-    if (top - lane >= range_start) { nxt_m = masks[top - lane]; nxt_g = flatten_ids[top - lane]; }
-    while (more || r_tail - r_head > 0) {
-        if (more) {
-            // ---- gather 32 entries of the tile list (back to front), keep those that can reach this patch
-            // (the forward stored every staged entry's patch mask: non-reaching entries cost one byte load)
-            const int pos = top - lane;
-            const unsigned hit = (pos >= range_start) ? ((nxt_m >> wid) & 1u) : 0u;
-            const int g = nxt_g;
-            top -= 32;
-            more = top >= range_start;
-            if (top - lane >= range_start) { nxt_m = masks[top - lane]; nxt_g = flatten_ids[top - lane]; }
-            float4 e0, e1;
-            if (hit) {
-                const float4 r0 = __ldg(rec + 2 * (size_t)g), r1 = __ldg(rec + 2 * (size_t)g + 1);
-                e0 = make_float4(r0.x, r0.y, 0.5f * GSB_NEG_LOG2E * r1.x, GSB_NEG_LOG2E * r1.y);
-                e1 = make_float4(0.5f * GSB_NEG_LOG2E * r1.z, r0.w, r0.z, __int_as_float(pos));
-            }
-            const unsigned bits = __ballot_sync(0xffffffffu, hit);
-            if (hit) {
-                const int slot = (r_tail + __popc(bits & lt_mask)) & 63;
-                ws.rec[slot][0] = e0; ws.rec[slot][1] = e1; ws.gid[slot] = g;
-            }
-            r_tail += __popc(bits);
-            __syncwarp();
-        }
-        // ---- consume steps of eight compacted entries (a partial last step is padded with dead entries)
-        while (r_tail - r_head >= 8 || (!more && r_tail - r_head > 0)) {
-            const int avail = r_tail - r_head;
-            const int sA = (r_head + 2 * gq) & 63, sB = (r_head + 2 * gq + 1) & 63;
-            float4 a0 = ws.rec[sA][0], a1 = ws.rec[sA][1], b0 = ws.rec[sB][0], b1 = ws.rec[sB][1];
-            if (2 * gq >= avail) { a0 = make_float4(0.f, 0.f, 0.f, 0.f); a1 = make_float4(0.f, 0.f, 0.f, __int_as_float(0x7fffffff)); }
-            if (2 * gq + 1 >= avail) { b0 = make_float4(0.f, 0.f, 0.f, 0.f); b1 = make_float4(0.f, 0.f, 0.f, __int_as_float(0x7fffffff)); }
-            const int posA = __float_as_int(a1.w), posB = __float_as_int(b1.w);
-            // per-Gaussian terms shared by the four pixels of the column: sigma' = qa + dy * (qb + qc * dy)
-            const float dxA = a0.x - px, dxB = b0.x - px;
-            const float qaA = a0.z * dxA * dxA, qbA = a0.w * dxA, qaB = b0.z * dxB * dxB, qbB = b0.w * dxB;
-            const float dyA0 = a0.y - py0, dyB0 = b0.y - py0;
-            float mA0 = 0.f, mA1 = 0.f, mA2 = 0.f, mAd = 0.f, mB0 = 0.f, mB1 = 0.f, mB2 = 0.f, mBd = 0.f;
-#pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                const float dyA = dyA0 - (float)r, dyB = dyB0 - (float)r;
-                const float sgA = fmaf(dyA, fmaf(a1.x, dyA, qbA), qaA), sgB = fmaf(dyB, fmaf(b1.x, dyB, qbB), qaB);
-                float visA, visB;
-                asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(visA) : "f"(sgA));
-                asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(visB) : "f"(sgB));
-                const float ovA = a1.y * visA, ovB = b1.y * visB;
-                const float alA0 = fminf(GSB_ALPHA_MAX, ovA), alB0 = fminf(GSB_ALPHA_MAX, ovB);
-                const bool okA = (posA <= bin_final[r]) && !(sgA > 0.f) && !(alA0 < GSB_ALPHA_MIN);
-                const bool okB = (posB <= bin_final[r]) && !(sgB > 0.f) && !(alB0 < GSB_ALPHA_MIN);
-                // dead pairs get alpha = 0: every formula below then yields its neutral element without a branch
-                const float alA = okA ? alA0 : 0.f, alB = okB ? alB0 : 0.f;
-                const float wA = 1.f - alA, wB = 1.f - alB;             // 1 / ra  (>= 1e-3)
-                const float raA = rcp_fast(wA), raB = rcp_fast(wB);     // rcp(1) == 1
-                // inclusive scan of ra over the 8 Gaussians of the step: local pair, then the four lanes of the column
-                float inc = raA * raB;
-                float tsh = __shfl_up_sync(0xffffffffu, inc, 1, 4);
-                if (gq >= 1) inc *= tsh;
-                tsh = __shfl_up_sync(0xffffffffu, inc, 2, 4);
-                if (gq >= 2) inc *= tsh;
-                const float tot = __shfl_sync(0xffffffffu, inc, 3, 4);
-                const float TB = T[r] * inc;          // transmittance in front of B (after dividing B out)
-                const float TA = TB * wB;             // ... in front of A
-                T[r] *= tot;
-                const float facA = alA * TA, facB = alB * TB;
-                const float cA = a1.z * facA, cB = b1.z * facB;
-                const float loc = cA + cB;
-                float sinc = loc;
-                float ssh = __shfl_up_sync(0xffffffffu, sinc, 1, 4);
-                if (gq >= 1) sinc += ssh;
-                ssh = __shfl_up_sync(0xffffffffu, sinc, 2, 4);
-                if (gq >= 2) sinc += ssh;
-                const float stot = __shfl_sync(0xffffffffu, sinc, 3, 4);
-                const float bufA = buf[r] + (sinc - loc);   // sum of everything replayed before A
-                const float bufB = bufA + cA;
-                buf[r] += stot;
-                const float valA = (a1.z * TA - bufA * raA) * v_rc[r] + v_raT[r] * raA;
-                const float valB = (b1.z * TB - bufB * raB) * v_rc[r] + v_raT[r] * raB;
-                // v_sigma = -opac * vis * v_alpha, only where alpha is not clamped (A.5) and the pair is live
-                const float gA = (okA && ovA <= GSB_ALPHA_MAX) ? -ovA : 0.f, gB = (okB && ovB <= GSB_ALPHA_MAX) ? -ovB : 0.f;
-                const float vsA = gA * valA, vsB = gB * valB;
-                mAd = fmaf(facA, v_rc[r], mAd); mBd = fmaf(facB, v_rc[r], mBd);
-                mA0 += vsA; mB0 += vsB;
-                const float vdA = vsA * dyA, vdB = vsB * dyB;
-                mA1 += vdA; mB1 += vdB;
-                mA2 = fmaf(vdA, dyA, mA2); mB2 = fmaf(vdB, dyB, mB2);
-            }
-            // moments -> the six sums of this lane's column (conic back in its own units: a = a' / (-log2e/2) ...)
-            const float caA = a0.z * (2.f / GSB_NEG_LOG2E), cbA = a0.w * (1.f / GSB_NEG_LOG2E), ccA = a1.x * (2.f / GSB_NEG_LOG2E);
-            const float caB = b0.z * (2.f / GSB_NEG_LOG2E), cbB = b0.w * (1.f / GSB_NEG_LOG2E), ccB = b1.x * (2.f / GSB_NEG_LOG2E);
-            float v[12];
-            v[0] = caA * dxA * mA0 + cbA * mA1;  v[1] = cbA * dxA * mA0 + ccA * mA1;
-            v[2] = 0.5f * dxA * dxA * mA0;       v[3] = dxA * mA1;  v[4] = 0.5f * mA2;  v[5] = mAd;
-            v[6] = caB * dxB * mB0 + cbB * mB1;  v[7] = cbB * dxB * mB0 + ccB * mB1;
-            v[8] = 0.5f * dxB * dxB * mB0;       v[9] = dxB * mB1;  v[10] = 0.5f * mB2; v[11] = mBd;
-            // sum over the eight columns (lane bits 2..4): halve 12 -> 6 (A | B) -> 3, then a plain butterfly
-#pragma unroll
-            for (int k = 0; k < 6; ++k) {
-                const float keep = up16 ? v[k + 6] : v[k], send = up16 ? v[k] : v[k + 6];
-                v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-            }
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                const float keep = up8 ? v[k + 3] : v[k], send = up8 ? v[k] : v[k + 3];
-                v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-            }
-#pragma unroll
-            for (int k = 0; k < 3; ++k) v[k] += __shfl_xor_sync(0xffffffffu, v[k], 4);
-            if (!(lane & 4)) {   // lane (gq, bit16 -> A|B, bit8 -> components 0..2 | 3..5) writes three numbers
-                const int e = 2 * gq + (up16 ? 1 : 0);
-                const int slot = (q_tail + e) & 63;
-                float* dst = &ws.qsum[slot][up8 ? 3 : 0];
-                dst[0] = v[0]; dst[1] = v[1]; dst[2] = v[2];
-                if (!up8) ws.qid[slot] = (e < avail) ? ws.gid[(r_head + e) & 63] : -1;
-            }
-            r_head += min(avail, 8);
-            q_tail += 8;
-            __syncwarp();
-            if (q_tail - q_head >= 32) {
-                const int slot = (q_head + lane) & 63;
-                const int gid = ws.qid[slot];
-                if (gid >= 0)
-                    lift_to_pose(&s_ctx, gid, ws.qsum[slot][0], ws.qsum[slot][1], ws.qsum[slot][2], ws.qsum[slot][3],
-                                 ws.qsum[slot][4], ws.qsum[slot][5], pose_col, GSB_BWD_THREADS);
-                q_head += 32;
-                __syncwarp();
-            }
-        }
-    }
-    __syncwarp();
-    if (lane < q_tail - q_head) {
-        const int slot = (q_head + lane) & 63;
-        const int gid = ws.qid[slot];
-        if (gid >= 0)
-            lift_to_pose(&s_ctx, gid, ws.qsum[slot][0], ws.qsum[slot][1], ws.qsum[slot][2], ws.qsum[slot][3],
-                         ws.qsum[slot][4], ws.qsum[slot][5], pose_col, GSB_BWD_THREADS);
-    }
-    __syncthreads();
-    for (int k = lwid; k < 12; k += GSB_BWD_WARPS) {
-        float s = 0.f;
-#pragma unroll
-        for (int q = 0; q < GSB_BWD_WARPS; ++q) s += s_pose[k * GSB_BWD_THREADS + q * 32 + lane];
-        s = warp_sum(s);
-        if (lane == 0) partials[((size_t)bin * GSB_BWD_SPLIT + part) * 12 + k] = s;
-    }
-}
-
-
 // ------------------------------------------------------------------------------------------------------------------
-// Round 2: the same quad-scan replay with a third fewer issued instructions (both rasterisers sit on the SM's issue
-// roofline, profiles/r1_m_iteration_full.md).  What changed against raster_bwd_quad_kernel:
+// Tracker path: "quad-scan" replay, every warp an independent unit (no __syncthreads until the final reduction).
+//
+// A pixel-per-lane replay (the op-level kernel above) spends a third of its instructions on the 32-lane butterfly that
+// sums six numbers per Gaussian, and evaluates one (pixel, Gaussian) pair per lane per ~120 warp instructions.  Here the
+// warp's 8x4 patch is re-mapped: lane L = (column pr = L >> 2, Gaussian pair gq = L & 3) owns the FOUR pixels of column
+// pr and TWO of the eight Gaussians of a step, i.e. 8 pairs per lane per step with all Gaussian data in registers.
+//   * The sequential recurrences of A.5 along the Gaussian axis (T <- T / (1 - alpha), buffer <- buffer + d alpha T)
+//     are ONE affine scan: a two-element local combine plus two shuffle rounds over the four lanes of a column.
+//   * dx is shared by a lane's four pixels, so the five geometric gradients reduce to three moments of v_sigma
+//     (sum v, sum v dy, sum v dy^2) accumulated in registers.
+// The set of (pixel, Gaussian) pairs evaluated, the validity rules and every formula are those of the replay above;
+// only the association order of the per-pixel products / sums differs (1e-7 relative).  Entries are first compacted
+// (patch masks written by the forward) into a per-warp ring; a step consumes eight.
+//
+// Round 2 took a third of the issued instructions out of the round-1 version of this kernel (both rasterisers sit on
+// the SM's issue roofline, profiles/r1_m_iteration_full.md -> r2_*):
 //   * Gaussians A and B of a lane are the two halves of packed-fp32 registers: every statement of the row body that was
 //     written twice ("...A, ...B") is ONE FFMA2 / FMUL2 / FADD2 (Blackwell only; bit-identical per half).
 //   * 1 / (1 - alpha) of both Gaussians from ONE reciprocal: rr = rcp(wA * wB), raA = rr * wB, raB = rr * wA, and the
@@ -557,16 +331,16 @@ __global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad_
 //     the twelve sums are kept in CAMERA space (sum v_pc pc^T, sum v_pc); the block turns them into d loss / d viewmat
 //     once at the end: v_R = (S - v_t t^T) R, because mean = R^T (pc - t).
 // Same pairs evaluated, same validity rules, same formulas; association order of a few sums differs (1e-7 relative).
-#define Q2_TR_STEP 400   // words per step of the transposition buffer: 32 lanes x 12 floats + 16 (LDS.64 reads of the
+#define Q_TR_STEP 400   // words per step of the transposition buffer: 32 lanes x 12 floats + 16 (LDS.64 reads of the
                          // lift hit 16 different bank pairs per half warp; the STS.128 of the steps are conflict-free)
-struct Quad2Scratch {
+struct QuadScratch {
     // compaction ring, one array per field: a lane's Gaussians A and B are neighbouring slots, so ONE LDS.64 per field
     // lands {A, B} in the aligned register pair the packed instructions want (no MOVs to pair them up)
     float x[64], y[64], ca[64], cb[64], cc[64], op[64], dep[64];   // ca, cb, cc: pre-scaled conic a', b', c'
     float sc[64];                // first scale of the Gaussian (the lift of an isotropic map needs nothing else of it)
     int pos[64];                 // position in the tile's sorted list (0x7fffffff: padding)
     int gid[64];                 // flat Gaussian index (-1: padding)
-    float tr[4 * Q2_TR_STEP];
+    float tr[4 * Q_TR_STEP];
     // landing zone of the asynchronous gather (cp.async / LDGSTS, one slot per lane): the records of the NEXT 32 list
     // entries travel global -> shared while the current steps are being consumed, without holding registers
     float4 st_r0[32], st_r1[32];
@@ -610,15 +384,15 @@ __device__ __forceinline__ void lift_iso_cam(const LiftCtx* __restrict__ ctx, fl
     }
 }
 
-__global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad2_kernel(
+__global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad_kernel(
     int C, int N, int W, int H, int tile_w, int tile_h, const float4* __restrict__ rec,
     const int2* __restrict__ ranges, const int* __restrict__ flatten_ids,
     const float* __restrict__ render_alphas, const int* __restrict__ last_ids, const float* __restrict__ v_depth,
     const float* __restrict__ v_alpha_img, const float* __restrict__ means, const float* __restrict__ quats,
     const float* __restrict__ scales, const float* __restrict__ viewmats, const float* __restrict__ Ks, float eps2d,
     float* __restrict__ partials, const int* __restrict__ stop, const unsigned char* __restrict__ masks,
-    const int* __restrict__ iso_flag) {
-    __shared__ __align__(16) Quad2Scratch s_w[GSB_BWD_WARPS];
+    const int* __restrict__ iso_flag, int stripe_rank, int stripe_mask) {
+    __shared__ __align__(16) QuadScratch s_w[GSB_BWD_WARPS];
     __shared__ float s_pose[12 * GSB_BWD_THREADS];
     __shared__ LiftCtx s_ctxs[GSB_BWD_WARPS];   // one copy per warp: no block barrier before the loop
 
@@ -633,6 +407,11 @@ __global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad2
     const int i0 = blockIdx.y * 16 + (wid >> 1) * 4;              // first row of the patch
     const float px = (float)j + 0.5f, py0 = (float)i0 + 0.5f;
     const int bin = cam * tile_w * tile_h + tile_id;
+    if ((tile_id & stripe_mask) != stripe_rank) {
+        // tile-striped frame (row f3): another rank replays this tile; a zero partial keeps the sum over ranks exact
+        if (tid < 12) partials[((size_t)bin * GSB_BWD_SPLIT + part) * 12 + tid] = 0.f;
+        return;
+    }
     const int2 range = ranges[bin];
     const int range_start = range.x, range_end = range.y;
 
@@ -668,7 +447,7 @@ __global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad2
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) warp_bin_final = max(warp_bin_final, __shfl_xor_sync(0xffffffffu, warp_bin_final, o));
 
-    Quad2Scratch& ws = s_w[lwid];
+    QuadScratch& ws = s_w[lwid];
     float* const pose_col = s_pose + tid;
     int r_head = 0, r_tail = 0;   // compaction ring (uniform); r_head is a multiple of 8
     int pend = 0;                 // consumed steps whose sums wait in ws.tr (0..3); their entries are ring slots
@@ -676,7 +455,7 @@ __global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad2
     const unsigned lt_mask = (1u << lane) - 1u;
     // transposition addresses: this lane's 12 numbers of a step / its entry's numbers of the eight columns
     float* const tr_store = ws.tr + lane * 12;
-    const float* const tr_load = ws.tr + (lane >> 3) * Q2_TR_STEP + ((lane & 7) >> 1) * 12 + (lane & 1) * 6;
+    const float* const tr_load = ws.tr + (lane >> 3) * Q_TR_STEP + ((lane & 7) >> 1) * 12 + (lane & 1) * 6;
 
     const int first = min(range_end - 1, warp_bin_final);
     int top = first;                       // list position of lane 0 of the chunk whose records are in flight
@@ -811,7 +590,7 @@ __global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad2
                 const f2 t = f2mul(dx, m0), th = f2mul(t, f2s(0.5f)), mh = f2mul(m1, f2s(0.5f));
                 const f2 v0 = f2fma(ca, t, f2mul(cb, mh)), v1 = f2fma(cb, th, f2mul(qc, m1));
                 const f2 v2 = f2mul(dx, th), v3 = f2mul(dx, m1);
-                float4* dst = reinterpret_cast<float4*>(tr_store + pend * Q2_TR_STEP);
+                float4* dst = reinterpret_cast<float4*>(tr_store + pend * Q_TR_STEP);
                 dst[0] = make_float4(v0.x, v1.x, v2.x, v3.x);
                 dst[1] = make_float4(m2.x, md.x, v0.y, v1.y);
                 dst[2] = make_float4(v2.y, v3.y, m2.y, md.y);
@@ -879,18 +658,14 @@ void launch_raster_bwd_lift(int C, int N, int W, int H, int tile_w, int tile_h, 
                             const float* render_alphas, const int* last_ids, const float* v_depth,
                             const float* v_alpha, const float* means, const float* quats, const float* scales,
                             const float* viewmats, const float* Ks, float eps2d, float* partials, const int* stop,
-                            const unsigned char* masks, const int* iso_flag, cudaStream_t st) {
+                            const unsigned char* masks, const int* iso_flag, int stripe_rank, int stripe_world,
+                            cudaStream_t st) {
     if (C * tile_w * tile_h == 0) return;
     dim3 grid(tile_w * GSB_BWD_SPLIT, tile_h, C);
-    static const int variant = getenv("GSB_BWD_VARIANT") ? atoi(getenv("GSB_BWD_VARIANT")) : 2;   // A/B switch (1: round-1 kernel)
-    if (variant == 1)
-        raster_bwd_quad_kernel<<<grid, GSB_BWD_THREADS, 0, st>>>(C, N, W, H, tile_w, tile_h, rec, ranges,
-                                                 flatten_ids, render_alphas, last_ids, v_depth, v_alpha, means, quats,
-                                                 scales, viewmats, Ks, eps2d, partials, stop, masks, iso_flag);
-    else
-        raster_bwd_quad2_kernel<<<grid, GSB_BWD_THREADS, 0, st>>>(C, N, W, H, tile_w, tile_h, rec, ranges,
-                                                 flatten_ids, render_alphas, last_ids, v_depth, v_alpha, means, quats,
-                                                 scales, viewmats, Ks, eps2d, partials, stop, masks, iso_flag);
+    raster_bwd_quad_kernel<<<grid, GSB_BWD_THREADS, 0, st>>>(C, N, W, H, tile_w, tile_h, rec, ranges, flatten_ids,
+                                                             render_alphas, last_ids, v_depth, v_alpha, means, quats,
+                                                             scales, viewmats, Ks, eps2d, partials, stop, masks, iso_flag,
+                                                             stripe_rank, stripe_world - 1);
 }
 
 int launch_raster_bwd_soa(int cdim, int C, int N, int W, int H, int tile_w, int tile_h, const float* means2d,

@@ -63,6 +63,9 @@ struct gsb_tracker {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int64_t total_launches = 0;
     int64_t last_n_isects = 0;
+    // tile-striped single frame over `stripe_world` GPUs (row f3): this tracker owns the tiles with
+    // tile & (stripe_world - 1) == stripe_rank; 1 = the whole frame
+    int stripe_rank = 0, stripe_world = 1;
 };
 
 static const int kStages = 9;   // slots of gsb_tracker_profile; pose_begin, tile_scan and bin_emit are fused away (0)
@@ -76,42 +79,57 @@ static void invalidate_graph(gsb_tracker* t) {
     t->exec = nullptr; t->graph = nullptr; t->graph_valid = false;
 }
 
+// The iteration in three segments (the cuts are where a tile-striped frame exchanges data between ranks):
+//   A  projection + binning, tile sort, raster forward      -> ed / alpha / last_ids of the tiles this tracker owns
+//   B  loss (whole image), raster backward of the own tiles -> 12-float partials per half tile
+//   C  pose_finish: sum of all partials, pose gradient, early stop, 2 x Adam, next viewmat
 // ``marks`` (nullable): kStages + 1 events recorded around the kernels (profiling mode).
-static void enqueue_iteration(gsb_tracker* t, bool forward_only, cudaEvent_t* marks = nullptr) {
+static void enqueue_segment(gsb_tracker* t, int seg, cudaEvent_t* marks, int& mk) {
     cudaStream_t st = t->stream;
     const gsb_tracker_config& c = t->cfg;
     const int C = t->C, N = t->N;
-    int mk = 0;
-#define GSB_MARK() do { if (marks) cudaEventRecord(marks[mk++], st); } while (0)
-    GSB_MARK();
-    GSB_MARK();   // (pose_begin slot: the viewmats are written at set-up by ensure_capacity and afterwards by pose_finish)
-    // projection + scatter into fixed-capacity tile bins in ONE pass (no histogram, scan or second pass)
-    launch_project_emit(C, N, t->means, t->quats, t->scales, t->opac, t->viewmats, t->Ks, t->W, t->H, t->tile_w,
-                        t->tile_h, c.eps2d, c.near_plane, c.far_plane, c.radius_clip, t->rec, t->cursor, t->keys,
-                        t->tile_cap, t->n_isects, t->overflow, t->stop, st);
-    GSB_MARK();
-    GSB_MARK();   // (tile_scan slot)
-    GSB_MARK();   // (bin_emit slot)
-    launch_tile_sort_fixed(C, t->n_tiles, t->tile_cap, t->cursor, t->keys, t->flatten_ids, t->ranges, t->n_isects,
-                           t->stop, st);
-    GSB_MARK();
-    launch_raster_fwd_packed(C, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->ranges, t->flatten_ids,
-                             t->ed, t->alpha, t->last_ids, 1, t->stop, t->masks, st);
-    GSB_MARK();
-    if (forward_only) return;
     const float inv_p = 1.f / ((float)t->W * (float)t->H);
-    launch_loss(C, t->W, t->H, t->ed, t->alpha, t->gt, 0, 1, c.depth_lambda * inv_p,
-                (1.f - c.depth_lambda - c.normal_lambda) * inv_p, c.normal_lambda, c.normal_mode, t->Ks,
-                t->normal_rows, 1, t->v_depth, t->v_alpha, t->loss_partials, t->stop, t->gt_edge, st);
-    GSB_MARK();
-    launch_raster_bwd_lift(C, N, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->ranges, t->flatten_ids,
-                           t->alpha, t->last_ids, t->v_depth, t->v_alpha, t->means, t->quats, t->scales, t->viewmats,
-                           t->Ks, c.eps2d, t->partials, t->stop, t->masks, t->iso_flag, st);
-    GSB_MARK();
-    launch_pose_finish(C, t->n_tiles * raster_bwd_partials_per_tile(), t->n_loss_blocks, t->partials, t->loss_partials, t->viewmats, t->state, t->stop,
-                       c, inv_p, 1.f / (3.f * (float)t->H), t->history, t->history_cap, st);
-    GSB_MARK();
+#define GSB_MARK() do { if (marks) cudaEventRecord(marks[mk++], st); } while (0)
+    if (seg == 0) {
+        GSB_MARK();
+        GSB_MARK();   // (pose_begin slot: the viewmats are written at set-up by ensure_capacity and afterwards by pose_finish)
+        // projection + scatter into fixed-capacity tile bins in ONE pass (no histogram, scan or second pass)
+        launch_project_emit(C, N, t->means, t->quats, t->scales, t->opac, t->viewmats, t->Ks, t->W, t->H, t->tile_w,
+                            t->tile_h, c.eps2d, c.near_plane, c.far_plane, c.radius_clip, t->rec, t->cursor, t->keys,
+                            t->tile_cap, t->n_isects, t->overflow, t->stop, t->stripe_rank, t->stripe_world, st);
+        GSB_MARK();
+        GSB_MARK();   // (tile_scan slot)
+        GSB_MARK();   // (bin_emit slot)
+        launch_tile_sort_fixed(C, t->n_tiles, t->tile_cap, t->cursor, t->keys, t->flatten_ids, t->ranges, t->n_isects,
+                               t->stop, st);
+        GSB_MARK();
+        launch_raster_fwd_packed(C, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->ranges, t->flatten_ids,
+                                 t->ed, t->alpha, t->last_ids, 1, t->stop, t->masks, t->stripe_rank, t->stripe_world, st);
+        GSB_MARK();
+    } else if (seg == 1) {
+        launch_loss(C, t->W, t->H, t->ed, t->alpha, t->gt, 0, 1, c.depth_lambda * inv_p,
+                    (1.f - c.depth_lambda - c.normal_lambda) * inv_p, c.normal_lambda, c.normal_mode, t->Ks,
+                    t->normal_rows, 1, t->v_depth, t->v_alpha, t->loss_partials, t->stop, t->gt_edge, st);
+        GSB_MARK();
+        launch_raster_bwd_lift(C, N, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->ranges, t->flatten_ids,
+                               t->alpha, t->last_ids, t->v_depth, t->v_alpha, t->means, t->quats, t->scales, t->viewmats,
+                               t->Ks, c.eps2d, t->partials, t->stop, t->masks, t->iso_flag, t->stripe_rank,
+                               t->stripe_world, st);
+        GSB_MARK();
+    } else {
+        launch_pose_finish(C, t->n_tiles * raster_bwd_partials_per_tile(), t->n_loss_blocks, t->partials, t->loss_partials,
+                           t->viewmats, t->state, t->stop, c, inv_p, 1.f / (3.f * (float)t->H), t->history, t->history_cap, st);
+        GSB_MARK();
+    }
 #undef GSB_MARK
+}
+
+static void enqueue_iteration(gsb_tracker* t, bool forward_only, cudaEvent_t* marks = nullptr) {
+    int mk = 0;
+    enqueue_segment(t, 0, marks, mk);
+    if (forward_only) return;
+    enqueue_segment(t, 1, marks, mk);
+    enqueue_segment(t, 2, marks, mk);
 }
 
 // (Re)allocate the fixed-capacity tile bins: keys, sorted ids and patch masks for C * tiles * tile_cap entries.
@@ -549,6 +567,54 @@ int gsb_tracker_debug_limit_bins(gsb_tracker* t, int tile_cap) {
 }
 
 void* gsb_tracker_stream(gsb_tracker* t) { return t ? (void*)t->stream : nullptr; }
+
+// ---- tile-striped single frame over several GPUs
+int gsb_tracker_set_stripe(gsb_tracker* t, int rank, int world) {
+    if (!t || world < 1 || (world & (world - 1)) != 0 || rank < 0 || rank >= world)
+        return fail(GSB_ERR_ARG, "gsb_tracker_set_stripe: world must be a power of two and 0 <= rank < world", cudaSuccess);
+    t->stripe_rank = rank; t->stripe_world = world;
+    invalidate_graph(t);   // the stripe is a kernel argument
+    return GSB_OK;
+}
+
+int gsb_tracker_stripe_segment(gsb_tracker* t, int segment) {
+    if (!t || segment < 0 || segment > 2) return fail(GSB_ERR_ARG, "gsb_tracker_stripe_segment: segment must be 0, 1 or 2", cudaSuccess);
+    if (!t->have_map || !t->have_obs || !t->have_pose)
+        return fail(GSB_ERR_ARG, "gsb_tracker_stripe_segment: map, observation and poses must be set first", cudaSuccess);
+    if (segment == 0 && t->cap_dirty) {
+        int rc = ensure_capacity(t);
+        if (rc) return rc;
+    }
+    int mk = 0;
+    enqueue_segment(t, segment, nullptr, mk);
+    t->total_launches += segment == 0 ? 3 : (segment == 1 ? n_launches_per_iter(t) - 4 : 1);
+    return GSB_OK;
+}
+
+int gsb_tracker_stripe_buffers(gsb_tracker* t, void** render_depth, void** partials, int64_t* n_depth, int64_t* n_partials) {
+    if (!t) return fail(GSB_ERR_ARG, "gsb_tracker_stripe_buffers: null", cudaSuccess);
+    if (render_depth) *render_depth = t->ed;
+    if (partials) *partials = t->partials;
+    if (n_depth) *n_depth = (int64_t)t->C * t->W * t->H;
+    if (n_partials) *n_partials = (int64_t)t->C * t->n_tiles * 12 * raster_bwd_partials_per_tile();
+    return GSB_OK;
+}
+
+int gsb_tracker_stripe_finish(gsb_tracker* t, int* overflowed, int* all_stopped) {
+    if (!t) return fail(GSB_ERR_ARG, "gsb_tracker_stripe_finish: null", cudaSuccess);
+    cudaStream_t st = t->stream;
+    TCK(cudaMemcpyAsync(t->h_flags, t->stop, sizeof(int) * t->C, cudaMemcpyDeviceToHost, st), "flags");
+    TCK(cudaMemcpyAsync(t->h_flags + t->C, t->n_isects, sizeof(int) * 2, cudaMemcpyDeviceToHost, st), "flags");
+    TCK(cudaStreamSynchronize(st), "stripe sync");
+    TCK(cudaGetLastError(), "stripe");
+    t->last_n_isects = t->h_flags[t->C];
+    if (overflowed) *overflowed = t->h_flags[t->C + 1] != 0;
+    if (all_stopped) {
+        *all_stopped = 1;
+        for (int c = 0; c < t->C; ++c) *all_stopped &= (t->h_flags[c] != 0);
+    }
+    return GSB_OK;
+}
 
 int gsb_tracker_debug_loss_grads(gsb_tracker* t, float* v_depth, float* v_alpha) {
     if (!t) return fail(GSB_ERR_ARG, "gsb_tracker_debug_loss_grads: null", cudaSuccess);

@@ -178,6 +178,27 @@ int gsb_tracker_get_history(gsb_tracker* t, int camera, float* out_host, int max
 int gsb_tracker_get_counters(gsb_tracker* t, int64_t* n_isects, int64_t* capacity, int* launches_per_iter,
                              int64_t* total_launches);
 void* gsb_tracker_stream(gsb_tracker* t);
+
+/* ---- tile-striped single frame over several GPUs (BASELINE.json configs[4] on 8 GPUs; the shape of
+ * gsplat's rasterization(distributed=True), IDX:14882-14926, re-cut for one frame and a pose-only gradient).
+ * One tracker per GPU holds the WHOLE map and observation and owns the tiles with tile_id & (world - 1) == rank (world
+ * a power of two).  An iteration is three segments with one exchange after each of the first two:
+ *   segment 0  projection (all Gaussians, binned into the own tiles only), tile sort, raster forward; the tiles of other
+ *              ranks are written as ZEROS     -> all-reduce (sum) of the rendered depth image [C,H,W]
+ *   segment 1  loss on the whole image, raster backward of the own tiles; partials of other ranks' tiles are ZEROS
+ *                                              -> all-reduce (sum) of the partials
+ *   segment 2  pose_finish on every rank (same sums -> the same Adam step everywhere)
+ * Every element of both buffers is non-zero on at most one rank, so the sums are exact and the trajectory is bit-identical
+ * to the one-GPU run.  The caller owns the collectives (gsplatloc_b200/stripe.py: torch.distributed / NCCL on the
+ * tracker's stream). */
+int gsb_tracker_set_stripe(gsb_tracker* t, int rank, int world);
+/* enqueue one segment (no host synchronisation) */
+int gsb_tracker_stripe_segment(gsb_tracker* t, int segment);
+/* device pointers and element counts (float) of the two exchanged buffers */
+int gsb_tracker_stripe_buffers(gsb_tracker* t, void** render_depth, void** partials, int64_t* n_depth, int64_t* n_partials);
+/* synchronise; *overflowed != 0: a tile bin filled up (the iterations since are invalid: set the poses again);
+ * *all_stopped: every camera's early stop has fired */
+int gsb_tracker_stripe_finish(gsb_tracker* t, int* overflowed, int* all_stopped);
 /* copies of the tracker's intermediates for parity tests, into caller-allocated DEVICE buffers (any may be NULL):
  * sorted flatten_ids [M], tile offsets [C*T+1], projected records [C*N,8] = {x,y,depth,opacity,a,b,c,radius bits}.
  * The loop keeps one fixed-capacity bin per (camera, tile); this call compacts them into gsplat's layout

