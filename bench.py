@@ -353,6 +353,101 @@ def run_native(args, rank, world, local_rank):
     print(json.dumps(out), flush=True)
 
 
+def run_striped(args, rank, world, local_rank):
+    """--split tiles (BASELINE.json configs[4]): ONE frame, its tiles interleaved over the ranks
+    (gsplatloc_b200/stripe.py).  A step is the frame's ``--iters`` iterations; two all-reduces per iteration (rendered
+    depth image, per-tile pose partials) over NCCL / NVLink, no host synchronisation inside a step.  Strong scaling:
+    value = iterations/s of the one frame."""
+    import torch.distributed as dist
+    from gsplatloc_b200 import PoseTracker, TrackerConfig, _lib
+    from gsplatloc_b200.stripe import StripedTracker
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: gsplatloc_b200 has no CPU path")
+    _lib.lib()
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    K, W_, iters = args.steps, args.warmup, args.iters
+    fp = make_frames(args.workload, 1, seed0=42)[0]          # the same frame on every rank
+    N = fp.tar_points.shape[0]
+    stream = torch.cuda.Stream(dev)
+    obs = rendered_observation(PoseTracker, fp, dev, stream)
+    pin = dict(means=torch.tensor(fp.tar_points).pin_memory(), quats=torch.tensor([[1.0, 0, 0, 0]]).repeat(N, 1).pin_memory(),
+               scales=torch.tensor(fp.scales).pin_memory(), opac=torch.ones(N).pin_memory(), depth=obs.cpu().pin_memory())
+    trk = PoseTracker(fp.W, fp.H, 1, TrackerConfig(max_steps=args.max_steps, early_stop=False, depth_lambda=args.depth_lambda),
+                      device=dev, stream=stream)
+    trk.set_map(pin["means"].to(dev), pin["quats"].to(dev), pin["scales"].to(dev), pin["opac"].to(dev))
+    trk.set_observation(obs, fp.K)
+    st = StripedTracker(trk, rank, world)
+    trk.set_poses(fp.tar_c2w, fp.src_c2w)
+    st.iterate(2)                 # sizes the bins, warms NCCL up
+    st.finish()
+    if not args.no_stripe_graph:
+        st.capture()              # one CUDA graph per iteration: 6 kernels + 2 NCCL all-reduces
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def step(e2e):
+        if e2e:
+            trk.set_map(pin["means"], pin["quats"], pin["scales"], pin["opac"])
+            trk.set_observation(pin["depth"], fp.K)
+        trk.set_poses(fp.tar_c2w, fp.src_c2w)
+        st.iterate(iters)
+        st.finish()
+        return trk.states()[0] if e2e else None
+
+    out_ms = []
+    for e2e in (False, True):
+        for _ in range(max(W_, 1) if not e2e else 1):
+            step(e2e)
+        sampler = ClockSampler(local_rank) if (rank == 0 and not e2e) else None
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        w0 = time.time()
+        e0.record(stream)
+        for _ in range(K):
+            last = step(e2e)
+        e1.record(stream)
+        barrier()
+        w1 = time.time()
+        out_ms.append(e0.elapsed_time(e1))
+        if sampler:
+            clocks = sampler.stop(w0, w1)
+    ms, ms_e2e = out_ms
+    M_own = trk.counters()["n_isects"]
+    stt = trk.states()[0]
+    if world > 1:
+        tt = torch.tensor([ms, ms_e2e, float(M_own)], device=dev, dtype=torch.float64)
+        mx = tt.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = tt.clone(); dist.all_reduce(sm)
+        ms, ms_e2e, M_max, M_sum = float(mx[0]), float(mx[1]), int(mx[2]), int(sm[2])
+    else:
+        M_max = M_sum = M_own
+    if rank != 0:
+        return
+    value = K * iters / (ms * 1e-3)
+    h2d = int(sum(v.numel() * 4 for v in pin.values())) + 16 * 4 * 2 + 9 * 4
+    print(json.dumps({
+        "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W_,
+        "ms_per_step": round(ms / K, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": f"{args.workload}: {fp.W}x{fp.H}, N={N} Gaussians, M={M_sum} tile intersections, ONE frame, "
+                               f"tiles interleaved over {world} ranks, {iters} iterations per step (BASELINE.json configs[4])",
+                   "split": "tiles", "iters_per_step": iters, "isects_per_rank_max": M_max, "isects_per_rank_mean": M_sum // world,
+                   "collectives_per_iteration": 0 if world == 1 else 2, "cuda_graph": not args.no_stripe_graph,
+                   "nvlink_bytes_per_iteration_per_rank": int(st.nvlink_bytes_per_iter),
+                   "us_per_iteration": round(1e3 * ms / (K * iters), 2),
+                   "l2": "one frame resident; iterations reuse L2 as the real loop does",
+                   "timing": "CUDA events on the launching stream, barrier+synchronize both sides, max over ranks"},
+        "e2e": {"value": round(K * iters / (ms_e2e * 1e-3), 2), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": int(__import__("ctypes").sizeof(_lib.PoseState)), "ms_per_step": round(ms_e2e / K, 4)},
+        "gpu_launches": int(K * iters * 6 * world), "clocks": clocks,
+        "pose_errors": {"eT_m": float(stt["eT"]), "eR_deg": float(stt["eR"]), "loss": float(stt["loss"])},
+        "gsplat_cuda": probe_gsplat()}), flush=True)
+
+
 def run_dropin(args):
     """--api rasterization: the zero-code-change route of INTEGRATION.md §1 -- GsplatLoc's own loop shape with
     ``from gsplatloc_b200 import rasterization`` in place of gsplat's: CameraOptModule-style quaternion + translation
@@ -496,8 +591,10 @@ def main():
     ap.add_argument("--max-steps", type=int, default=2000, help="LR schedule horizon (GsplatLoc_eval.py --num-iters)")
     ap.add_argument("--pool", type=int, default=4, help="distinct frames cycled per rank")
     ap.add_argument("--cameras", type=int, default=1, help="pose hypotheses per frame (BASELINE.json configs[3]: 64)")
-    ap.add_argument("--split", default="frames", choices=["frames", "hypotheses"],
-                    help="what the ranks shard: independent frames (weak scaling) or the pose hypotheses of one frame (strong)")
+    ap.add_argument("--split", default="frames", choices=["frames", "hypotheses", "tiles"],
+                    help="what the ranks shard: independent frames (weak scaling), the pose hypotheses of one frame (strong) "
+                         "or the tiles of one frame (strong; two all-reduces per iteration)")
+    ap.add_argument("--no-stripe-graph", action="store_true", help="--split tiles: eager segments instead of one CUDA graph per iteration")
     ap.add_argument("--api", default="tracker", choices=["tracker", "rasterization"],
                     help="tracker: the device-resident loop (headline). rasterization: the drop-in route, one "
                          "gsplatloc_b200.rasterization() + torch autograd + torch Adam per iteration, as model.py:195-213 "
@@ -524,7 +621,10 @@ def main():
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:
-        run_native(args, rank, world, local_rank)
+        if args.split == "tiles":
+            run_striped(args, rank, world, local_rank)
+        else:
+            run_native(args, rank, world, local_rank)
     finally:
         if world > 1:
             import torch.distributed as dist

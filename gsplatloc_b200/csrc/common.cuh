@@ -256,6 +256,14 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
+// Tile-striped single frame over several GPUs: rank r owns the horizontal tile PAIRS (32x16 pixels:
+// four 32x8 loss blocks) whose index ty * ceil(tile_w / 2) + (tx >> 1) is r modulo the world size (a power of two;
+// stripe_mask = world - 1; 0 = one GPU owns everything).  Interleaved pairs balance the load, and a pair is the unit at
+// which the loss blocks and the raster tiles of one rank coincide.
+__device__ __forceinline__ bool stripe_owns(int tx, int ty, int tile_w, int stripe_rank, int stripe_mask) {
+    return ((ty * ((tile_w + 1) >> 1) + (tx >> 1)) & stripe_mask) == stripe_rank;
+}
+
 // Conservative 8-bit "patch mask" of one Gaussian inside a 16x16 tile whose first pixel is (tile_x0, tile_y0).
 // A warp of the raster kernels owns an 8x4 pixel patch: warp w covers columns 8*(w&1)..+7 and rows 4*(w>>1)..+3.
 // Bit w is set when the alpha >= 1/255 ellipse of the Gaussian (sigma <= ln(255*opacity), A.4) can reach a pixel

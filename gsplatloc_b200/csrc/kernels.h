@@ -84,7 +84,8 @@ void loss_grid(int W, int H, int* gx, int* gy);
 void launch_loss(int C, int W, int H, const float* ed, const float* alpha, const float* gt, size_t gt_cam_stride,
                  int apply_mask, float w_d, float w_s, float lambda_n, int normal_mode, const float* Ks,
                  float* normal_rows, int mode, float* v_out, float* v_alpha, float* partial, const int* stop,
-                 const float* gt_edge, cudaStream_t st);
+                 const float* gt_edge, int stripe_rank, int stripe_world, cudaStream_t st);
+bool loss_is_striped(float lambda_n, int LBX_check = 32);
 void launch_edge_magnitude(int W, int H, const float* img, float* out, cudaStream_t st);
 
 // ---- pose.cu

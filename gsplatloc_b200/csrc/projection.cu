@@ -198,6 +198,7 @@ void launch_project_bwd(int C, int N, const float* means, const float* quats, co
 // group's leader reserves room once per tile; boxes larger than 2 x 2 tiles are flattened over the warp.  A bin that
 // would overflow raises *overflow (the run is reported invalid and re-sized, tracker.cu).  Thread (0,0) clears the
 // intersection counter that tile_sort accumulates.
+template <bool STRIPED>
 __global__ void __launch_bounds__(256) project_emit_kernel(
     int C, int N, const float* __restrict__ means, const float* __restrict__ quats, const float* __restrict__ scales,
     const float* __restrict__ opacities, const float* __restrict__ viewmats, const float* __restrict__ Ks, int W, int H,
@@ -206,8 +207,8 @@ __global__ void __launch_bounds__(256) project_emit_kernel(
     int* __restrict__ n_isects, int* __restrict__ overflow, const int* __restrict__ stop, int stripe_rank,
     int stripe_mask) {
     // Tile-striped single frame over several GPUs: every rank projects all Gaussians but bins
-    // only into the tiles it owns, tile & stripe_mask == stripe_rank (stripe_mask = world - 1, world a power of two;
-    // 0 = one GPU: every tile).  The records are written for every Gaussian either way.
+    // only into the tiles it owns (common.cuh stripe_owns; stripe_mask = world - 1, 0 = one GPU: every tile).  The
+    // records are written for every Gaussian either way.
     __shared__ int s_incl[8][32];
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     const int c = blockIdx.y;
@@ -244,10 +245,10 @@ __global__ void __launch_bounds__(256) project_emit_kernel(
     if (small) {
         const int leader = __ffs(grp) - 1, cnt = __popc(grp), rank = __popc(grp & ((1u << lane) - 1u));
         const int t00 = y0 * tile_w + x0;
-        const bool o0 = (t00 & stripe_mask) == stripe_rank;
-        const bool hx = bw > 1 && ((t00 + 1) & stripe_mask) == stripe_rank;
-        const bool hy = bh > 1 && ((t00 + tile_w) & stripe_mask) == stripe_rank;
-        const bool hxy = bw > 1 && bh > 1 && ((t00 + tile_w + 1) & stripe_mask) == stripe_rank;
+        const bool o0 = !STRIPED || stripe_owns((int)x0, (int)y0, tile_w, stripe_rank, stripe_mask);
+        const bool hx = bw > 1 && (!STRIPED || stripe_owns((int)x0 + 1, (int)y0, tile_w, stripe_rank, stripe_mask));
+        const bool hy = bh > 1 && (!STRIPED || stripe_owns((int)x0, (int)y0 + 1, tile_w, stripe_rank, stripe_mask));
+        const bool hxy = bw > 1 && bh > 1 && (!STRIPED || stripe_owns((int)x0 + 1, (int)y0 + 1, tile_w, stripe_rank, stripe_mask));
         int b0 = 0, b1 = 0, b2 = 0, b3 = 0;
         if (lane == leader) {
             if (o0) b0 = atomicAdd(cur + t00, cnt);
@@ -293,8 +294,9 @@ __global__ void __launch_bounds__(256) project_emit_kernel(
             bool mine_t = false;
             if (w < total) {
                 const uint32_t t = (uint32_t)(w - sexcl);
-                tile = (int)((sy0 + t / sbw) * tile_w + sx0 + t % sbw);
-                mine_t = (tile & stripe_mask) == stripe_rank;
+                const int tyy = (int)(sy0 + t / sbw), txx = (int)(sx0 + t % sbw);
+                tile = tyy * tile_w + txx;
+                mine_t = !STRIPED || stripe_owns(txx, tyy, tile_w, stripe_rank, stripe_mask);
                 if (!mine_t) tile = -1 - lane;   // not this rank's tile: no group, no atomic
             }
             const unsigned g2 = __match_any_sync(0xffffffffu, tile);
@@ -318,9 +320,14 @@ void launch_project_emit(int C, int N, const float* means, const float* quats, c
                          int stripe_rank, int stripe_world, cudaStream_t st) {
     if (N == 0 || C == 0) return;
     dim3 grid((N + 255) / 256, C);
-    project_emit_kernel<<<grid, 256, 0, st>>>(C, N, means, quats, scales, opacities, viewmats, Ks, W, H, tile_w, tile_h,
-                                              eps2d, near_plane, far_plane, radius_clip, rec, cursor, keys, tile_cap,
-                                              n_isects, overflow, stop, stripe_rank, stripe_world - 1);
+    if (stripe_world > 1)
+        project_emit_kernel<true><<<grid, 256, 0, st>>>(C, N, means, quats, scales, opacities, viewmats, Ks, W, H, tile_w,
+                                                        tile_h, eps2d, near_plane, far_plane, radius_clip, rec, cursor, keys,
+                                                        tile_cap, n_isects, overflow, stop, stripe_rank, stripe_world - 1);
+    else
+        project_emit_kernel<false><<<grid, 256, 0, st>>>(C, N, means, quats, scales, opacities, viewmats, Ks, W, H, tile_w,
+                                                         tile_h, eps2d, near_plane, far_plane, radius_clip, rec, cursor, keys,
+                                                         tile_cap, n_isects, overflow, stop, 0, 0);
 }
 
 void launch_project_bin(int C, int N, const float* means, const float* quats, const float* scales,

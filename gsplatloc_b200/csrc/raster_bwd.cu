@@ -407,7 +407,7 @@ __global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad_
     const int i0 = blockIdx.y * 16 + (wid >> 1) * 4;              // first row of the patch
     const float px = (float)j + 0.5f, py0 = (float)i0 + 0.5f;
     const int bin = cam * tile_w * tile_h + tile_id;
-    if ((tile_id & stripe_mask) != stripe_rank) {
+    if (!stripe_owns(tile_x, blockIdx.y, tile_w, stripe_rank, stripe_mask)) {
         // tile-striped frame (row f3): another rank replays this tile; a zero partial keeps the sum over ranks exact
         if (tid < 12) partials[((size_t)bin * GSB_BWD_SPLIT + part) * 12 + tid] = 0.f;
         return;

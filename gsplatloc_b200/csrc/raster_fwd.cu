@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(256) raster_fwd_pair_kernel(
     const float tile_x0 = (float)(blockIdx.x * 16), tile_y0 = (float)(blockIdx.y * 16);
     const bool inside = (i < H) && (j < W);
     const int bin = cam * tile_w * tile_h + tile_id;
-    if ((tile_id & stripe_mask) != stripe_rank) {
+    if (!stripe_owns(blockIdx.x, blockIdx.y, tile_w, stripe_rank, stripe_mask)) {
         // tile-striped frame (row f3): another rank renders this tile; zeros here make the sum over ranks (all-reduce
         // of the image) bit-identical to a single-GPU render
         if (inside) {

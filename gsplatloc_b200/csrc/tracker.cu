@@ -109,7 +109,8 @@ static void enqueue_segment(gsb_tracker* t, int seg, cudaEvent_t* marks, int& mk
     } else if (seg == 1) {
         launch_loss(C, t->W, t->H, t->ed, t->alpha, t->gt, 0, 1, c.depth_lambda * inv_p,
                     (1.f - c.depth_lambda - c.normal_lambda) * inv_p, c.normal_lambda, c.normal_mode, t->Ks,
-                    t->normal_rows, 1, t->v_depth, t->v_alpha, t->loss_partials, t->stop, t->gt_edge, st);
+                    t->normal_rows, 1, t->v_depth, t->v_alpha, t->loss_partials, t->stop, t->gt_edge, t->stripe_rank,
+                    t->stripe_world, st);
         GSB_MARK();
         launch_raster_bwd_lift(C, N, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->ranges, t->flatten_ids,
                                t->alpha, t->last_ids, t->v_depth, t->v_alpha, t->means, t->quats, t->scales, t->viewmats,
@@ -255,8 +256,9 @@ static int tracker_alloc(gsb_tracker* t, int C, int W, int H, void* stream) {
     TCK(cudaMalloc(&t->v_depth, sizeof(float) * P), "alloc");
     TCK(cudaMalloc(&t->v_alpha, sizeof(float) * P), "alloc");
     TCK(cudaMalloc(&t->last_ids, sizeof(int) * P), "alloc");
-    TCK(cudaMalloc(&t->partials, sizeof(float) * nb * 12 * raster_bwd_partials_per_tile()), "alloc");
-    TCK(cudaMalloc(&t->loss_partials, sizeof(float) * (size_t)C * t->n_loss_blocks * 3), "alloc");
+    // pose partials and loss partials share one allocation: a tile-striped frame sums both over the ranks in one collective
+    TCK(cudaMalloc(&t->partials, sizeof(float) * (nb * 12 * raster_bwd_partials_per_tile() + (size_t)C * t->n_loss_blocks * 3)), "alloc");
+    t->loss_partials = t->partials + nb * 12 * raster_bwd_partials_per_tile();
     TCK(cudaMalloc(&t->normal_rows, sizeof(float) * (size_t)C * H * 9), "alloc");
     TCK(cudaMalloc(&t->history, sizeof(float) * (size_t)t->history_cap * C * 8), "alloc");
     TCK(cudaMallocHost(&t->h_flags, sizeof(int) * (C + 2)), "alloc pinned");
@@ -291,7 +293,7 @@ void gsb_tracker_destroy(gsb_tracker* t) {
     invalidate_graph(t);
     void* bufs[] = {t->means, t->quats, t->scales, t->opac, t->gt, t->gt_edge, t->Ks, t->viewmats, t->state, t->stop, t->rec,
                     t->bbox, t->counts, t->offsets, t->cursor, t->ranges, t->n_isects, t->keys, t->flatten_ids, t->masks, t->ed, t->alpha,
-                    t->v_depth, t->v_alpha, t->last_ids, t->partials, t->loss_partials, t->normal_rows,
+                    t->v_depth, t->v_alpha, t->last_ids, t->partials, t->normal_rows,
                     t->history, t->state_bak, t->viewmats_bak, t->stop_bak};
     for (void* b : bufs)
         if (b) cudaFree(b);
@@ -578,13 +580,14 @@ int gsb_tracker_set_stripe(gsb_tracker* t, int rank, int world) {
 }
 
 int gsb_tracker_stripe_segment(gsb_tracker* t, int segment) {
-    if (!t || segment < 0 || segment > 2) return fail(GSB_ERR_ARG, "gsb_tracker_stripe_segment: segment must be 0, 1 or 2", cudaSuccess);
+    if (!t || segment < -1 || segment > 2) return fail(GSB_ERR_ARG, "gsb_tracker_stripe_segment: segment must be -1 ... 2", cudaSuccess);
     if (!t->have_map || !t->have_obs || !t->have_pose)
         return fail(GSB_ERR_ARG, "gsb_tracker_stripe_segment: map, observation and poses must be set first", cudaSuccess);
-    if (segment == 0 && t->cap_dirty) {
+    if ((segment == 0 || segment == -1) && t->cap_dirty) {   // new map / poses: viewmats from the poses, bins sized (synchronises)
         int rc = ensure_capacity(t);
         if (rc) return rc;
     }
+    if (segment == -1) return GSB_OK;
     int mk = 0;
     enqueue_segment(t, segment, nullptr, mk);
     t->total_launches += segment == 0 ? 3 : (segment == 1 ? n_launches_per_iter(t) - 4 : 1);
@@ -596,7 +599,10 @@ int gsb_tracker_stripe_buffers(gsb_tracker* t, void** render_depth, void** parti
     if (render_depth) *render_depth = t->ed;
     if (partials) *partials = t->partials;
     if (n_depth) *n_depth = (int64_t)t->C * t->W * t->H;
-    if (n_partials) *n_partials = (int64_t)t->C * t->n_tiles * 12 * raster_bwd_partials_per_tile();
+    // the loss partials follow the pose partials in memory; they take part in the sum when the loss kernel is striped too
+    if (n_partials)
+        *n_partials = (int64_t)t->C * t->n_tiles * 12 * raster_bwd_partials_per_tile() +
+                      (loss_is_striped(t->cfg.normal_lambda) ? (int64_t)t->C * t->n_loss_blocks * 3 : 0);
     return GSB_OK;
 }
 

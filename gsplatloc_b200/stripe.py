@@ -4,10 +4,11 @@ GsplatLoc's path, where the only gradient is the 6-DoF pose and the loss couples
 
 * every rank holds the whole map and the observation and projects ALL Gaussians (replicating the 73 us projection of
   2 M Gaussians is cheaper than gathering 66 MB of records over NVLink, ~95 us at the measured 770 GB/s);
-* rank r bins, sorts and rasterises only the tiles with ``tile_id & (world - 1) == r`` (interleaved: balanced);
+* rank r bins, sorts and rasterises only the horizontal tile pairs (32x16 pixels) whose index is r modulo ``world``
+  (interleaved: balanced; a pair holds four 32x8 loss blocks, so the loss kernel is striped the same way);
 * the rendered depth image is summed over ranks (``all_reduce``: each pixel is non-zero on one rank, so the sum is
-  exact), every rank evaluates the loss on the whole image, replays its own tiles, and the per-tile pose partials are
-  summed the same way; ``pose_finish`` then takes the identical Adam step on every rank.
+  exact), every rank evaluates the loss blocks of its own tile pairs (their 2-pixel halo comes from the summed image),
+  replays its own tiles, and the per-tile pose partials and per-block loss partials are summed the same way; ``pose_finish`` then takes the identical Adam step on every rank.
 
 Two collectives per iteration, both exact, so the trajectory is bit-identical to the one-GPU tracker's.  The
 collectives run through ``torch.distributed`` (NCCL over NVLink on the GPU box) on the tracker's stream, with no host
@@ -57,18 +58,40 @@ class StripedTracker:
     def segment(self, k: int):
         _lib.check(self._L.gsb_tracker_stripe_segment(self.trk._h, int(k)), "tracker_stripe_segment")
 
+    def _one_iteration(self):
+        self.segment(0)
+        if self.world > 1:
+            self._all_reduce(self.depth)
+        self.segment(1)
+        if self.world > 1:
+            self._all_reduce(self.partials)
+        self.segment(2)
+
+    def capture(self):
+        """Record one iteration -- five kernel segments' launches and the two NCCL collectives -- as ONE CUDA graph on
+        the tracker's stream (torch's graph capture; NCCL collectives are capturable).  Call after at least one eager
+        iteration at the current frame size (the first segment sizes the tile bins, which synchronises).  The graph is
+        dropped when the bins are re-sized."""
+        self._graph, self._graph_cap = None, self.trk.counters()["capacity"]
+        g = torch.cuda.CUDAGraph()
+        torch.cuda.synchronize(self.trk.device)
+        with torch.cuda.graph(g, stream=self.trk.stream):
+            self._one_iteration()
+        self._graph = g
+
     def iterate(self, n: int):
-        """``n`` iterations, nothing but enqueues: 3 segments + 2 collectives each, all on the tracker's stream."""
-        stream = self.trk.stream
-        with torch.cuda.stream(stream):
+        """``n`` iterations, nothing but enqueues on the tracker's stream: one graph launch each when ``capture`` has
+        been called, else 3 segment calls + 2 collectives."""
+        self.segment(-1)   # after set_poses / set_map: viewmats and bin sizes (a no-op otherwise)
+        g = getattr(self, "_graph", None)
+        if g is not None and self.trk.counters()["capacity"] != self._graph_cap:
+            g = self._graph = None
+        with torch.cuda.stream(self.trk.stream):
             for _ in range(n):
-                self.segment(0)
-                if self.world > 1:
-                    self._all_reduce(self.depth)
-                self.segment(1)
-                if self.world > 1:
-                    self._all_reduce(self.partials)
-                self.segment(2)
+                if g is not None:
+                    g.replay()
+                else:
+                    self._one_iteration()
 
     def finish(self) -> dict:
         over, stopped = ctypes.c_int(0), ctypes.c_int(0)

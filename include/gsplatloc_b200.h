@@ -181,18 +181,20 @@ void* gsb_tracker_stream(gsb_tracker* t);
 
 /* ---- tile-striped single frame over several GPUs (BASELINE.json configs[4] on 8 GPUs; the shape of
  * gsplat's rasterization(distributed=True), IDX:14882-14926, re-cut for one frame and a pose-only gradient).
- * One tracker per GPU holds the WHOLE map and observation and owns the tiles with tile_id & (world - 1) == rank (world
- * a power of two).  An iteration is three segments with one exchange after each of the first two:
+ * One tracker per GPU holds the WHOLE map and observation and owns the horizontal tile pairs (32x16 pixels) whose
+ * index ty * ceil(tile_w / 2) + (tx >> 1) is rank modulo world (world a power of two).  An iteration is three segments with one exchange after each of the first two:
  *   segment 0  projection (all Gaussians, binned into the own tiles only), tile sort, raster forward; the tiles of other
  *              ranks are written as ZEROS     -> all-reduce (sum) of the rendered depth image [C,H,W]
- *   segment 1  loss on the whole image, raster backward of the own tiles; partials of other ranks' tiles are ZEROS
- *                                              -> all-reduce (sum) of the partials
+ *   segment 1  loss on the 32x8 blocks of the own tile pairs (whole image when the normal term is on), raster backward of
+ *              the own tiles; partials of other ranks' tiles and blocks are ZEROS
+ *                                              -> all-reduce (sum) of the pose partials + loss partials (one buffer)
  *   segment 2  pose_finish on every rank (same sums -> the same Adam step everywhere)
  * Every element of both buffers is non-zero on at most one rank, so the sums are exact and the trajectory is bit-identical
  * to the one-GPU run.  The caller owns the collectives (gsplatloc_b200/stripe.py: torch.distributed / NCCL on the
  * tracker's stream). */
 int gsb_tracker_set_stripe(gsb_tracker* t, int rank, int world);
-/* enqueue one segment (no host synchronisation) */
+/* enqueue one segment (no host synchronisation).  segment -1: only the set-up that segment 0 does after new poses / a new
+ * map (viewmats from the poses, bin sizing: synchronises) -- call it before replaying a captured iteration */
 int gsb_tracker_stripe_segment(gsb_tracker* t, int segment);
 /* device pointers and element counts (float) of the two exchanged buffers */
 int gsb_tracker_stripe_buffers(gsb_tracker* t, void** render_depth, void** partials, int64_t* n_depth, int64_t* n_partials);
