@@ -381,8 +381,12 @@ def run_striped(args, rank, world, local_rank):
     trk.set_poses(fp.tar_c2w, fp.src_c2w)
     st.iterate(2)                 # sizes the bins, warms NCCL up
     st.finish()
+    if args.stripe_fused:
+        st.fuse()                 # peer stores from the kernels + two barrier kernels instead of two NCCL all-reduces
+        st.iterate(2)
+        st.finish()
     if not args.no_stripe_graph:
-        st.capture()              # one CUDA graph per iteration: 6 kernels + 2 NCCL all-reduces
+        st.capture()              # one CUDA graph per iteration: 6 kernels + 2 exchanges
 
     def barrier():
         if world > 1:
@@ -436,7 +440,8 @@ def run_striped(args, rank, world, local_rank):
         "config": {"workload": f"{args.workload}: {fp.W}x{fp.H}, N={N} Gaussians, M={M_sum} tile intersections, ONE frame, "
                                f"tiles interleaved over {world} ranks, {iters} iterations per step (BASELINE.json configs[4])",
                    "split": "tiles", "iters_per_step": iters, "isects_per_rank_max": M_max, "isects_per_rank_mean": M_sum // world,
-                   "collectives_per_iteration": 0 if world == 1 else 2, "cuda_graph": not args.no_stripe_graph,
+                   "collectives_per_iteration": 0 if (world == 1 or args.stripe_fused) else 2, "cuda_graph": not args.no_stripe_graph,
+                   "exchange": "none" if world == 1 else ("fused peer stores + 2 barrier kernels" if args.stripe_fused else "2 NCCL all-reduces"),
                    "nvlink_bytes_per_iteration_per_rank": int(st.nvlink_bytes_per_iter),
                    "us_per_iteration": round(1e3 * ms / (K * iters), 2),
                    "l2": "one frame resident; iterations reuse L2 as the real loop does",
@@ -594,6 +599,7 @@ def main():
     ap.add_argument("--split", default="frames", choices=["frames", "hypotheses", "tiles"],
                     help="what the ranks shard: independent frames (weak scaling), the pose hypotheses of one frame (strong) "
                          "or the tiles of one frame (strong; two all-reduces per iteration)")
+    ap.add_argument("--stripe-fused", action="store_true", help="--split tiles: fused exchange (kernels store into every rank's buffers over NVLink, barrier kernels) instead of NCCL all-reduces")
     ap.add_argument("--no-stripe-graph", action="store_true", help="--split tiles: eager segments instead of one CUDA graph per iteration")
     ap.add_argument("--api", default="tracker", choices=["tracker", "rasterization"],
                     help="tracker: the device-resident loop (headline). rasterization: the drop-in route, one "

@@ -81,6 +81,11 @@ _SIGS = {
     "gsb_tracker_stripe_segment": (c_i, [c_p, c_i]),
     "gsb_tracker_stripe_buffers": (c_i, [c_p, c_p, c_p, c_p, c_p]),
     "gsb_tracker_stripe_finish": (c_i, [c_p, c_p, c_p]),
+    "gsb_tracker_stripe_exchange_buffers": (c_i, [c_p, c_p, c_p, c_p]),
+    "gsb_tracker_stripe_set_peers": (c_i, [c_p, c_i, c_p, c_p, c_p]),
+    "gsb_ipc_export": (c_i, [c_p, c_p]),
+    "gsb_ipc_open": (c_i, [c_p, c_p]),
+    "gsb_ipc_close": (c_i, [c_p]),
     "gsb_knn_sq_dists": (c_i, [c_i, c_p, c_i, c_p, C.POINTER(c_i), c_p]),
     "gsb_init_gs_scales": (c_i, [c_i, c_p, c_i, c_f, c_i, c_p, c_p]),
     "gsb_depth_to_points": (c_i, [c_i, c_i, c_p, C.POINTER(c_f), C.POINTER(c_f), c_p, c_p]),

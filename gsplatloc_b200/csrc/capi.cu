@@ -211,7 +211,7 @@ int gsb_depth_edge_loss(int C, int width, int height, const float* depth, const 
     int gx, gy;
     loss_grid(width, height, &gx, &gy);
     launch_loss(C, width, height, depth, nullptr, gt, gt_per_camera ? (size_t)width * height : 0, apply_mask, w_d,
-                w_s, 0.f, 0, nullptr, nullptr, 0, v_depth, nullptr, partial_ws, nullptr, nullptr, 0, 1, st);
+                w_s, 0.f, 0, nullptr, nullptr, 0, v_depth, nullptr, partial_ws, nullptr, nullptr, Stripe(), st);
     reduce_loss_partials_kernel<<<C, 256, 0, st>>>(gx * gy, partial_ws, loss_sums, 2);
     CK_LAUNCH("gsb_depth_edge_loss");
     return GSB_OK;
@@ -235,7 +235,7 @@ int gsb_depth_edge_normal_loss(int C, int width, int height, const float* depth,
     float* rows = ws + (size_t)3 * C * gx * gy;
     // lambda_n == 0 switches the term off inside launch_loss; keep the cosine sum defined (0) in that case
     launch_loss(C, width, height, depth, nullptr, gt, gt_per_camera ? (size_t)width * height : 0, apply_mask, w_d,
-                w_s, lambda_n, normal_mode, Ks, rows, 0, v_depth, nullptr, ws, nullptr, nullptr, 0, 1, st);
+                w_s, lambda_n, normal_mode, Ks, rows, 0, v_depth, nullptr, ws, nullptr, nullptr, Stripe(), st);
     reduce_loss_partials_kernel<<<C, 256, 0, st>>>(gx * gy, ws, loss_sums, 3);
     CK_LAUNCH("gsb_depth_edge_normal_loss");
     return GSB_OK;

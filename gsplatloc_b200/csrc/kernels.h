@@ -8,6 +8,16 @@
 
 namespace gsb {
 
+// Tile-striped frame over several GPUs.  rank / mask: the owner test (common.cuh stripe_owns; mask =
+// world - 1, 0 = one GPU owns everything).  n_peers > 0 selects the FUSED exchange: a kernel stores what it produces for its
+// own tiles straight into the same buffer of EVERY rank (peer[r], own included; NVLink peer stores) instead of leaving
+// zeros for a later all-reduce; tiles of other ranks are then not touched at all.
+struct Stripe {
+    int rank = 0, mask = 0, n_peers = 0;
+    float* const* peer = nullptr;   // DEVICE array of n_peers buffer pointers (a table in global memory: indexing a by-value
+                                    // array with a run-time index would push the kernel parameters onto the local stack)
+};
+
 // ---- projection.cu
 void launch_project_fwd(int C, int N, const float* means, const float* quats, const float* scales,
                         const float* viewmats, const float* Ks, int W, int H, float eps2d, float near_plane,
@@ -60,7 +70,7 @@ void launch_compact_bins(int n_bins, const int2* ranges, const int* padded, cons
 void launch_raster_fwd_packed(int C, int W, int H, int tile_w, int tile_h, const float4* rec, const int2* ranges,
                               const int* flatten_ids, float* render_depth,
                               float* render_alphas, int* last_ids, int normalize, const int* stop,
-                              unsigned char* masks_out, int stripe_rank, int stripe_world, cudaStream_t st);
+                              unsigned char* masks_out, const Stripe& stripe, cudaStream_t st);
 int launch_raster_fwd_soa(int cdim, int C, int W, int H, int tile_w, int tile_h, const float* means2d,
                           const float* conics, const float* colors, const float* opacities, const float* backgrounds,
                           const int* tile_offsets, int n_isects, const int* flatten_ids, float* render_colors,
@@ -70,8 +80,7 @@ void launch_raster_bwd_lift(int C, int N, int W, int H, int tile_w, int tile_h, 
                             const float* render_alphas, const int* last_ids, const float* v_depth,
                             const float* v_alpha, const float* means, const float* quats, const float* scales,
                             const float* viewmats, const float* Ks, float eps2d, float* partials, const int* stop,
-                            const unsigned char* masks, const int* iso_flag, int stripe_rank, int stripe_world,
-                            cudaStream_t st);
+                            const unsigned char* masks, const int* iso_flag, const Stripe& stripe, cudaStream_t st);
 void launch_map_iso(int N, const float* scales, int* flag, cudaStream_t st);
 int launch_raster_bwd_soa(int cdim, int C, int N, int W, int H, int tile_w, int tile_h, const float* means2d,
                           const float* conics, const float* colors, const float* opacities, const float* backgrounds,
@@ -84,7 +93,7 @@ void loss_grid(int W, int H, int* gx, int* gy);
 void launch_loss(int C, int W, int H, const float* ed, const float* alpha, const float* gt, size_t gt_cam_stride,
                  int apply_mask, float w_d, float w_s, float lambda_n, int normal_mode, const float* Ks,
                  float* normal_rows, int mode, float* v_out, float* v_alpha, float* partial, const int* stop,
-                 const float* gt_edge, int stripe_rank, int stripe_world, cudaStream_t st);
+                 const float* gt_edge, const Stripe& stripe, cudaStream_t st, size_t stripe_loss_offset = 0);
 bool loss_is_striped(float lambda_n, int LBX_check = 32);
 void launch_edge_magnitude(int W, int H, const float* img, float* out, cudaStream_t st);
 

@@ -353,7 +353,7 @@ __global__ void __launch_bounds__(LBX* LBY) loss_kernel(
 __global__ void __launch_bounds__(LBX* LBY) loss_track_kernel(
     int W, int H, const float* __restrict__ ed, const float* __restrict__ alpha, const float* __restrict__ gt,
     const float* __restrict__ gt_edge, float w_d, float w_s, float* __restrict__ v_out, float* __restrict__ v_alpha,
-    float* __restrict__ partial, const int* __restrict__ stop, int tile_w, int stripe_rank, int stripe_mask) {
+    float* __restrict__ partial, const int* __restrict__ stop, int tile_w, const Stripe stripe, size_t peer_offset) {
     __shared__ float sA[LH * LW], sB[LH * LW];
     __shared__ float sKx[(LBY + 2) * (LBX + 2)], sKy[(LBY + 2) * (LBX + 2)];
     __shared__ float s_red[2][(LBX * LBY) / 32];
@@ -363,10 +363,11 @@ __global__ void __launch_bounds__(LBX* LBY) loss_track_kernel(
     const int x0 = blockIdx.x * LBX, y0 = blockIdx.y * LBY;
     const int cam_off = cam * H * W;
     const float* d_img = ed + cam_off;
-    if (!stripe_owns(2 * blockIdx.x, blockIdx.y >> 1, tile_w, stripe_rank, stripe_mask)) {
+    if (!stripe_owns(2 * blockIdx.x, blockIdx.y >> 1, tile_w, stripe.rank, stripe.mask)) {
         // tile-striped frame (row f3): this 32x8 block lies in another rank's tile pair; zero partial sums keep the sum
-        // over ranks exact, and nobody reads d loss / d(D, alpha) of these pixels on this rank
-        if (tid < 3) partial[((cam * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 3 + tid] = 0.f;
+        // over ranks exact (fused exchange: the owner stores them here itself), and nobody reads d loss / d(D, alpha) of
+        // these pixels on this rank
+        if (tid < 3 && stripe.n_peers == 0) partial[((cam * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 3 + tid] = 0.f;
         return;
     }
 
@@ -495,7 +496,12 @@ __global__ void __launch_bounds__(LBX* LBY) loss_track_kernel(
             for (int w = 0; w < (LBX * LBY) / 32; ++w) t += s_red[tid][w];
         }
         const int blk = (cam * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
-        partial[blk * 3 + tid] = t;
+        if (stripe.n_peers == 0) {
+            partial[blk * 3 + tid] = t;
+        } else {   // fused exchange: the loss partials follow the pose partials in every rank's buffer
+#pragma unroll 1
+            for (int r = 0; r < stripe.n_peers; ++r) stripe.peer[r][peer_offset + blk * 3 + tid] = t;
+        }
     }
 }
 
@@ -513,7 +519,7 @@ void loss_grid(int W, int H, int* gx, int* gy) {
 void launch_loss(int C, int W, int H, const float* ed, const float* alpha, const float* gt, size_t gt_cam_stride,
                  int apply_mask, float w_d, float w_s, float lambda_n, int normal_mode, const float* Ks,
                  float* normal_rows, int mode, float* v_out, float* v_alpha, float* partial, const int* stop,
-                 const float* gt_edge, int stripe_rank, int stripe_world, cudaStream_t st) {
+                 const float* gt_edge, const Stripe& stripe, cudaStream_t st, size_t stripe_loss_offset) {
     if (C * W * H == 0) return;
     int gx, gy;
     loss_grid(W, H, &gx, &gy);
@@ -521,8 +527,10 @@ void launch_loss(int C, int W, int H, const float* ed, const float* alpha, const
     if (lambda_n == 0.f) normal_mode = 0;
     if (normal_mode == 0 && gt_edge && apply_mask && mode == 1 && gt_cam_stride == 0 && LBX == 32 &&
         (long long)C * W * H < (1ll << 31)) {   // the tracker's configuration: the lean kernel
+        // (fused stripe exchange: stripe.peer[r] is rank r's pose-partials buffer, which the loss partials follow)
+        const size_t peer_offset = stripe.n_peers ? stripe_loss_offset : 0;
         loss_track_kernel<<<grid, block, 0, st>>>(W, H, ed, alpha, gt, gt_edge, w_d, w_s, v_out, v_alpha, partial, stop,
-                                                  (W + GSB_TILE - 1) / GSB_TILE, stripe_rank, stripe_world - 1);
+                                                  (W + GSB_TILE - 1) / GSB_TILE, stripe, peer_offset);
         return;
     }
     if (normal_mode == 2) {

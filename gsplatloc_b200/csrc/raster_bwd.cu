@@ -391,7 +391,7 @@ __global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad_
     const float* __restrict__ v_alpha_img, const float* __restrict__ means, const float* __restrict__ quats,
     const float* __restrict__ scales, const float* __restrict__ viewmats, const float* __restrict__ Ks, float eps2d,
     float* __restrict__ partials, const int* __restrict__ stop, const unsigned char* __restrict__ masks,
-    const int* __restrict__ iso_flag, int stripe_rank, int stripe_mask) {
+    const int* __restrict__ iso_flag, const Stripe stripe) {
     __shared__ __align__(16) QuadScratch s_w[GSB_BWD_WARPS];
     __shared__ float s_pose[12 * GSB_BWD_THREADS];
     __shared__ LiftCtx s_ctxs[GSB_BWD_WARPS];   // one copy per warp: no block barrier before the loop
@@ -407,9 +407,10 @@ __global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad_
     const int i0 = blockIdx.y * 16 + (wid >> 1) * 4;              // first row of the patch
     const float px = (float)j + 0.5f, py0 = (float)i0 + 0.5f;
     const int bin = cam * tile_w * tile_h + tile_id;
-    if (!stripe_owns(tile_x, blockIdx.y, tile_w, stripe_rank, stripe_mask)) {
-        // tile-striped frame (row f3): another rank replays this tile; a zero partial keeps the sum over ranks exact
-        if (tid < 12) partials[((size_t)bin * GSB_BWD_SPLIT + part) * 12 + tid] = 0.f;
+    if (!stripe_owns(tile_x, blockIdx.y, tile_w, stripe.rank, stripe.mask)) {
+        // tile-striped frame (row f3): another rank replays this tile.  A zero partial keeps the sum over ranks exact; with
+        // the fused exchange the owner stores the partial into this rank's buffer itself.
+        if (tid < 12 && stripe.n_peers == 0) partials[((size_t)bin * GSB_BWD_SPLIT + part) * 12 + tid] = 0.f;
         return;
     }
     const int2 range = ranges[bin];
@@ -649,7 +650,13 @@ __global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad_
             out = (s_sum[i * 3 + 0] - vt * t[0]) * R[0 * 3 + jj] + (s_sum[i * 3 + 1] - vt * t[1]) * R[1 * 3 + jj] +
                   (s_sum[i * 3 + 2] - vt * t[2]) * R[2 * 3 + jj];
         }
-        partials[((size_t)bin * GSB_BWD_SPLIT + part) * 12 + tid] = out;
+        const size_t slot = ((size_t)bin * GSB_BWD_SPLIT + part) * 12 + tid;
+        if (stripe.n_peers == 0) {
+            partials[slot] = out;
+        } else {   // fused exchange: into the partials of every rank (peer[rank] is the own buffer)
+#pragma unroll 1
+            for (int r = 0; r < stripe.n_peers; ++r) stripe.peer[r][slot] = out;
+        }
     }
 }
 
@@ -658,14 +665,12 @@ void launch_raster_bwd_lift(int C, int N, int W, int H, int tile_w, int tile_h, 
                             const float* render_alphas, const int* last_ids, const float* v_depth,
                             const float* v_alpha, const float* means, const float* quats, const float* scales,
                             const float* viewmats, const float* Ks, float eps2d, float* partials, const int* stop,
-                            const unsigned char* masks, const int* iso_flag, int stripe_rank, int stripe_world,
-                            cudaStream_t st) {
+                            const unsigned char* masks, const int* iso_flag, const Stripe& stripe, cudaStream_t st) {
     if (C * tile_w * tile_h == 0) return;
     dim3 grid(tile_w * GSB_BWD_SPLIT, tile_h, C);
     raster_bwd_quad_kernel<<<grid, GSB_BWD_THREADS, 0, st>>>(C, N, W, H, tile_w, tile_h, rec, ranges, flatten_ids,
                                                              render_alphas, last_ids, v_depth, v_alpha, means, quats,
-                                                             scales, viewmats, Ks, eps2d, partials, stop, masks, iso_flag,
-                                                             stripe_rank, stripe_world - 1);
+                                                             scales, viewmats, Ks, eps2d, partials, stop, masks, iso_flag, stripe);
 }
 
 int launch_raster_bwd_soa(int cdim, int C, int N, int W, int H, int tile_w, int tile_h, const float* means2d,

@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(256) raster_fwd_pair_kernel(
     int W, int H, int tile_w, int tile_h, const float4* __restrict__ rec, const int2* __restrict__ ranges,
     const int* __restrict__ flatten_ids, float* __restrict__ render_depth, float* __restrict__ render_alphas,
     int* __restrict__ last_ids, int normalize_last, const int* __restrict__ stop,
-    unsigned char* __restrict__ masks_out, int stripe_rank, int stripe_mask) {
+    unsigned char* __restrict__ masks_out, const Stripe stripe) {
     // staged entries of the tile, one array per field; a', b', c' = the conic pre-scaled for ex2
     __shared__ float sx[FP_CHUNK], sy[FP_CHUNK], sa[FP_CHUNK], sb[FP_CHUNK], sc[FP_CHUNK], so[FP_CHUNK], sd[FP_CHUNK];
     __shared__ unsigned char s_mask[FP_CHUNK];
@@ -161,10 +161,11 @@ __global__ void __launch_bounds__(256) raster_fwd_pair_kernel(
     const float tile_x0 = (float)(blockIdx.x * 16), tile_y0 = (float)(blockIdx.y * 16);
     const bool inside = (i < H) && (j < W);
     const int bin = cam * tile_w * tile_h + tile_id;
-    if (!stripe_owns(blockIdx.x, blockIdx.y, tile_w, stripe_rank, stripe_mask)) {
-        // tile-striped frame (row f3): another rank renders this tile; zeros here make the sum over ranks (all-reduce
-        // of the image) bit-identical to a single-GPU render
-        if (inside) {
+    if (!stripe_owns(blockIdx.x, blockIdx.y, tile_w, stripe.rank, stripe.mask)) {
+        // tile-striped frame (row f3): another rank renders this tile.  Fused exchange: its owner stores the pixels into
+        // this rank's image itself.  Otherwise zeros here make the sum over ranks (all-reduce of the image) bit-identical
+        // to a single-GPU render.
+        if (inside && stripe.n_peers == 0) {
             const size_t pix = ((size_t)cam * H + i) * W + j;
             render_alphas[pix] = 0.f; render_depth[pix] = 0.f; last_ids[pix] = 0;
         }
@@ -261,7 +262,15 @@ __global__ void __launch_bounds__(256) raster_fwd_pair_kernel(
         const size_t pix = ((size_t)cam * H + i) * W + j;
         const float alpha = 1.f - Tfin;
         render_alphas[pix] = alpha;
-        render_depth[pix] = normalize_last ? out / fmaxf(alpha, 1e-10f) : out;   // "ED": A.4 / rendering.py
+        const float ed = normalize_last ? out / fmaxf(alpha, 1e-10f) : out;   // "ED": A.4 / rendering.py
+        if (stripe.n_peers == 0) {
+            render_depth[pix] = ed;
+        } else {
+            // fused compute + collective: the pixel goes straight into the depth image of every rank (peer stores over
+            // NVLink; the own image is peer[rank]) -- no all-reduce, the transfer overlaps the rest of the kernel
+#pragma unroll 1
+            for (int r = 0; r < stripe.n_peers; ++r) stripe.peer[r][pix] = ed;
+        }
         last_ids[pix] = cur_idx;
     }
 }
@@ -269,12 +278,11 @@ __global__ void __launch_bounds__(256) raster_fwd_pair_kernel(
 void launch_raster_fwd_packed(int C, int W, int H, int tile_w, int tile_h, const float4* rec, const int2* ranges,
                               const int* flatten_ids, float* render_depth,
                               float* render_alphas, int* last_ids, int normalize, const int* stop,
-                              unsigned char* masks_out, int stripe_rank, int stripe_world, cudaStream_t st) {
+                              unsigned char* masks_out, const Stripe& stripe, cudaStream_t st) {
     if (C * tile_w * tile_h == 0) return;
     dim3 grid(tile_w, tile_h, C);
     raster_fwd_pair_kernel<<<grid, 256, 0, st>>>(W, H, tile_w, tile_h, rec, ranges, flatten_ids, render_depth,
-                                                 render_alphas, last_ids, normalize, stop, masks_out, stripe_rank,
-                                                 stripe_world - 1);
+                                                 render_alphas, last_ids, normalize, stop, masks_out, stripe);
 }
 
 int launch_raster_fwd_soa(int cdim, int C, int W, int H, int tile_w, int tile_h, const float* means2d,

@@ -63,10 +63,43 @@ struct gsb_tracker {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int64_t total_launches = 0;
     int64_t last_n_isects = 0;
-    // tile-striped single frame over `stripe_world` GPUs (row f3): this tracker owns the tiles with
-    // tile & (stripe_world - 1) == stripe_rank; 1 = the whole frame
+    // tile-striped single frame over `stripe_world` GPUs (row f3): this tracker owns the tile pairs stripe_owns() gives
+    // to stripe_rank; 1 = the whole frame
     int stripe_rank = 0, stripe_world = 1;
+    // fused exchange (gsb_tracker_stripe_set_peers): every rank's depth image, partials buffer and barrier flags, as
+    // pointers valid on THIS device (the own ones at [stripe_rank]); n_peers == 0: the caller all-reduces instead
+    int n_peers = 0;
+    bool peer_barrier = false;     // false: all ranks share one stream of one device (tests): stream order is the barrier
+    float* peer_ed[8] = {};
+    float* peer_partials[8] = {};
+    int* peer_flags[8] = {};
+    int* stripe_flags = nullptr;   // [2 barriers][8 ranks] arrival epochs written by the peers, then [2] own epoch counters
+    int* stripe_error = nullptr;   // set when a barrier gives up waiting (a peer died): reported by stripe_finish
 };
+
+// Barrier between the ranks of a striped frame, inside the captured iteration: thread r tells rank r that everything this
+// rank has stored so far (its tiles' pixels / partials, peer stores of the kernel before) is complete, then waits until
+// rank r has said the same.  Epochs instead of a reset: the counter lives on the device, so a graph replay needs no new
+// arguments.  Each GPU runs its own stream; nobody waits on a kernel of the same device (B200_PROFILING.md).
+__global__ void stripe_barrier_kernel(int world, int rank, int slot, int* own_flags, int* const* peer_flags,
+                                      int* epochs, int* error) {
+    __shared__ int s_epoch;
+    if (threadIdx.x == 0) s_epoch = ++epochs[slot];
+    __syncthreads();
+    const int e = s_epoch, r = threadIdx.x;
+    if (r >= world) return;
+    __threadfence_system();                                    // the stores of the kernels before, system-wide
+    volatile int* theirs = peer_flags[r] + slot * 8 + rank;    // my arrival slot in rank r's flags
+    *theirs = e;
+    __threadfence_system();
+    volatile int* mine = own_flags + slot * 8 + r;
+    const long long t0 = clock64();
+    while (*mine < e) {
+        if (clock64() - t0 > 4000000000ll) { *error = 1; break; }   // ~2 s: a peer is gone; do not hang the GPU
+    }
+    __threadfence_system();
+}
+
 
 static const int kStages = 9;   // slots of gsb_tracker_profile; pose_begin, tile_scan and bin_emit are fused away (0)
 static int n_launches_per_iter(const gsb_tracker* t) {
@@ -84,8 +117,28 @@ static void invalidate_graph(gsb_tracker* t) {
 //   B  loss (whole image), raster backward of the own tiles -> 12-float partials per half tile
 //   C  pose_finish: sum of all partials, pose gradient, early stop, 2 x Adam, next viewmat
 // ``marks`` (nullable): kStages + 1 events recorded around the kernels (profiling mode).
+// device tables behind the barrier flags: [0] peers' flag words, [1] peers' depth images, [2] peers' partials
+static void** stripe_table(const gsb_tracker* t, int which) {
+    return reinterpret_cast<void**>(reinterpret_cast<char*>(t->stripe_flags) + sizeof(int) * 32) + 8 * which;
+}
+
+static Stripe stripe_of(const gsb_tracker* t, int which) {
+    Stripe sp;
+    sp.rank = t->stripe_rank; sp.mask = t->stripe_world - 1; sp.n_peers = t->n_peers;
+    sp.peer = reinterpret_cast<float* const*>(stripe_table(t, which));
+    return sp;
+}
+
+static void enqueue_stripe_barrier(gsb_tracker* t, int slot) {
+    // device copy of the peers' flag pointers lives behind the flags themselves (see gsb_tracker_stripe_set_peers)
+    int** d_peer_flags = reinterpret_cast<int**>(stripe_table(t, 0));
+    stripe_barrier_kernel<<<1, 32, 0, t->stream>>>(t->stripe_world, t->stripe_rank, slot, t->stripe_flags, d_peer_flags,
+                                                   t->stripe_flags + 16, t->stripe_error);
+}
+
 static void enqueue_segment(gsb_tracker* t, int seg, cudaEvent_t* marks, int& mk) {
     cudaStream_t st = t->stream;
+    const Stripe sp_ed = stripe_of(t, 1), sp_part = stripe_of(t, 2);
     const gsb_tracker_config& c = t->cfg;
     const int C = t->C, N = t->N;
     const float inv_p = 1.f / ((float)t->W * (float)t->H);
@@ -104,19 +157,20 @@ static void enqueue_segment(gsb_tracker* t, int seg, cudaEvent_t* marks, int& mk
                                t->stop, st);
         GSB_MARK();
         launch_raster_fwd_packed(C, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->ranges, t->flatten_ids,
-                                 t->ed, t->alpha, t->last_ids, 1, t->stop, t->masks, t->stripe_rank, t->stripe_world, st);
+                                 t->ed, t->alpha, t->last_ids, 1, t->stop, t->masks, sp_ed, st);
         GSB_MARK();
+        if (t->n_peers && t->peer_barrier) enqueue_stripe_barrier(t, 0);   // every rank's pixels have arrived in this image
     } else if (seg == 1) {
         launch_loss(C, t->W, t->H, t->ed, t->alpha, t->gt, 0, 1, c.depth_lambda * inv_p,
                     (1.f - c.depth_lambda - c.normal_lambda) * inv_p, c.normal_lambda, c.normal_mode, t->Ks,
-                    t->normal_rows, 1, t->v_depth, t->v_alpha, t->loss_partials, t->stop, t->gt_edge, t->stripe_rank,
-                    t->stripe_world, st);
+                    t->normal_rows, 1, t->v_depth, t->v_alpha, t->loss_partials, t->stop, t->gt_edge, sp_part, st,
+                    (size_t)(t->loss_partials - t->partials));
         GSB_MARK();
         launch_raster_bwd_lift(C, N, t->W, t->H, t->tile_w, t->tile_h, t->rec, t->ranges, t->flatten_ids,
                                t->alpha, t->last_ids, t->v_depth, t->v_alpha, t->means, t->quats, t->scales, t->viewmats,
-                               t->Ks, c.eps2d, t->partials, t->stop, t->masks, t->iso_flag, t->stripe_rank,
-                               t->stripe_world, st);
+                               t->Ks, c.eps2d, t->partials, t->stop, t->masks, t->iso_flag, sp_part, st);
         GSB_MARK();
+        if (t->n_peers && t->peer_barrier) enqueue_stripe_barrier(t, 1);   // every rank's partials have arrived
     } else {
         launch_pose_finish(C, t->n_tiles * raster_bwd_partials_per_tile(), t->n_loss_blocks, t->partials, t->loss_partials,
                            t->viewmats, t->state, t->stop, c, inv_p, 1.f / (3.f * (float)t->H), t->history, t->history_cap, st);
@@ -266,6 +320,10 @@ static int tracker_alloc(gsb_tracker* t, int C, int W, int H, void* stream) {
     TCK(cudaMemsetAsync(t->stop, 0, sizeof(int) * C, t->stream), "memset");
     TCK(cudaMemsetAsync(t->n_isects, 0, sizeof(int) * 3, t->stream), "memset");
     TCK(cudaMemsetAsync(t->partials, 0, sizeof(float) * nb * 12 * raster_bwd_partials_per_tile(), t->stream), "memset");
+    // striped-frame exchange state: [2][8] arrival epochs, [2] own epochs (+ padding), 3 tables of 8 peer pointers, 1 error word
+    TCK(cudaMalloc(&t->stripe_flags, sizeof(int) * 32 + sizeof(void*) * 24 + sizeof(int) * 4), "alloc");
+    TCK(cudaMemsetAsync(t->stripe_flags, 0, sizeof(int) * 32 + sizeof(void*) * 24 + sizeof(int) * 4, t->stream), "memset");
+    t->stripe_error = reinterpret_cast<int*>(reinterpret_cast<char*>(t->stripe_flags) + sizeof(int) * 32 + sizeof(void*) * 24);
     TCK(cudaEventCreate(&t->ev0), "event");
     TCK(cudaEventCreate(&t->ev1), "event");
     return GSB_OK;
@@ -294,7 +352,7 @@ void gsb_tracker_destroy(gsb_tracker* t) {
     void* bufs[] = {t->means, t->quats, t->scales, t->opac, t->gt, t->gt_edge, t->Ks, t->viewmats, t->state, t->stop, t->rec,
                     t->bbox, t->counts, t->offsets, t->cursor, t->ranges, t->n_isects, t->keys, t->flatten_ids, t->masks, t->ed, t->alpha,
                     t->v_depth, t->v_alpha, t->last_ids, t->partials, t->normal_rows,
-                    t->history, t->state_bak, t->viewmats_bak, t->stop_bak};
+                    t->history, t->state_bak, t->viewmats_bak, t->stop_bak, t->stripe_flags};
     for (void* b : bufs)
         if (b) cudaFree(b);
     if (t->h_flags) cudaFreeHost(t->h_flags);
@@ -606,13 +664,67 @@ int gsb_tracker_stripe_buffers(gsb_tracker* t, void** render_depth, void** parti
     return GSB_OK;
 }
 
+int gsb_tracker_stripe_exchange_buffers(gsb_tracker* t, void** render_depth, void** partials, void** flags) {
+    if (!t) return fail(GSB_ERR_ARG, "gsb_tracker_stripe_exchange_buffers: null", cudaSuccess);
+    if (render_depth) *render_depth = t->ed;
+    if (partials) *partials = t->partials;
+    if (flags) *flags = t->stripe_flags;
+    return GSB_OK;
+}
+
+int gsb_tracker_stripe_set_peers(gsb_tracker* t, int n, void* const* render_depth, void* const* partials, void* const* flags) {
+    if (!t || n < 0 || n > 8 || (n && (n != t->stripe_world || !render_depth || !partials)))
+        return fail(GSB_ERR_ARG, "gsb_tracker_stripe_set_peers: one pointer per rank of the stripe (world <= 8), or n = 0", cudaSuccess);
+    for (int r = 0; r < n; ++r) {
+        t->peer_ed[r] = (float*)render_depth[r];
+        t->peer_partials[r] = (float*)partials[r];
+        t->peer_flags[r] = flags ? (int*)flags[r] : nullptr;
+    }
+    if (n && (t->peer_ed[t->stripe_rank] != t->ed || t->peer_partials[t->stripe_rank] != t->partials))
+        return fail(GSB_ERR_ARG, "gsb_tracker_stripe_set_peers: entry [rank] must be this tracker's own buffer", cudaSuccess);
+    t->n_peers = n;
+    t->peer_barrier = n > 0 && flags != nullptr;
+    TCK(cudaMemcpyAsync(stripe_table(t, 0), t->peer_flags, sizeof(void*) * 8, cudaMemcpyHostToDevice, t->stream), "peer tables");
+    TCK(cudaMemcpyAsync(stripe_table(t, 1), t->peer_ed, sizeof(void*) * 8, cudaMemcpyHostToDevice, t->stream), "peer tables");
+    TCK(cudaMemcpyAsync(stripe_table(t, 2), t->peer_partials, sizeof(void*) * 8, cudaMemcpyHostToDevice, t->stream), "peer tables");
+    TCK(cudaMemsetAsync(t->stripe_flags, 0, sizeof(int) * 32, t->stream), "flags");
+    TCK(cudaMemsetAsync(t->stripe_error, 0, sizeof(int), t->stream), "flags");
+    TCK(cudaStreamSynchronize(t->stream), "peer tables sync");   // (the tables are member arrays: safe either way)
+    invalidate_graph(t);
+    return GSB_OK;
+}
+
+int gsb_ipc_export(const void* device_ptr, void* handle64) {
+    if (!device_ptr || !handle64) return fail(GSB_ERR_ARG, "gsb_ipc_export: null", cudaSuccess);
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    TCK(cudaIpcGetMemHandle((cudaIpcMemHandle_t*)handle64, const_cast<void*>(device_ptr)), "cudaIpcGetMemHandle");
+    return GSB_OK;
+}
+
+int gsb_ipc_open(const void* handle64, void** device_ptr) {
+    if (!device_ptr || !handle64) return fail(GSB_ERR_ARG, "gsb_ipc_open: null", cudaSuccess);
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, sizeof h);
+    TCK(cudaIpcOpenMemHandle(device_ptr, h, cudaIpcMemLazyEnablePeerAccess), "cudaIpcOpenMemHandle");
+    return GSB_OK;
+}
+
+int gsb_ipc_close(void* device_ptr) {
+    if (device_ptr) TCK(cudaIpcCloseMemHandle(device_ptr), "cudaIpcCloseMemHandle");
+    return GSB_OK;
+}
+
 int gsb_tracker_stripe_finish(gsb_tracker* t, int* overflowed, int* all_stopped) {
     if (!t) return fail(GSB_ERR_ARG, "gsb_tracker_stripe_finish: null", cudaSuccess);
     cudaStream_t st = t->stream;
     TCK(cudaMemcpyAsync(t->h_flags, t->stop, sizeof(int) * t->C, cudaMemcpyDeviceToHost, st), "flags");
     TCK(cudaMemcpyAsync(t->h_flags + t->C, t->n_isects, sizeof(int) * 2, cudaMemcpyDeviceToHost, st), "flags");
+    int barrier_error = 0;
+    TCK(cudaMemcpyAsync(&barrier_error, t->stripe_error, sizeof(int), cudaMemcpyDeviceToHost, st), "flags");
     TCK(cudaStreamSynchronize(st), "stripe sync");
     TCK(cudaGetLastError(), "stripe");
+    if (barrier_error)
+        return fail(GSB_ERR_CUDA, "gsb_tracker_stripe_finish: a rank of the striped frame did not reach a barrier within 2 s", cudaSuccess);
     t->last_n_isects = t->h_flags[t->C];
     if (overflowed) *overflowed = t->h_flags[t->C + 1] != 0;
     if (all_stopped) {

@@ -10,9 +10,11 @@ GsplatLoc's path, where the only gradient is the 6-DoF pose and the loss couples
   exact), every rank evaluates the loss blocks of its own tile pairs (their 2-pixel halo comes from the summed image),
   replays its own tiles, and the per-tile pose partials and per-block loss partials are summed the same way; ``pose_finish`` then takes the identical Adam step on every rank.
 
-Two collectives per iteration, both exact, so the trajectory is bit-identical to the one-GPU tracker's.  The
-collectives run through ``torch.distributed`` (NCCL over NVLink on the GPU box) on the tracker's stream, with no host
-synchronisation inside the loop.
+Two exchanges per iteration, both exact, so the trajectory is bit-identical to the one-GPU tracker's.  Two
+implementations: (1) all-reduces through ``torch.distributed`` (NCCL over NVLink on the GPU box) on the tracker's
+stream; (2) ``fuse()``: the kernels that produce the data store it straight into every rank's buffers (peer stores over
+NVLink, CUDA IPC) and a barrier kernel follows -- compute and collective in one kernel, no library call in the loop.
+Neither synchronises with the host inside the loop.
 """
 from __future__ import annotations
 
@@ -55,15 +57,72 @@ class StripedTracker:
         self._all_reduce = all_reduce
         self.nvlink_bytes_per_iter = 2 * (world - 1) / world * 4 * (nd.value + npar.value) if world > 1 else 0
 
+    # ------------------------------------------------------------------ fused exchange (peer stores instead of all-reduce)
+    def _own_exchange_buffers(self):
+        d, p, f = ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_void_p()
+        _lib.check(self._L.gsb_tracker_stripe_exchange_buffers(self.trk._h, ctypes.byref(d), ctypes.byref(p), ctypes.byref(f)),
+                   "tracker_stripe_exchange_buffers")
+        return d.value, p.value, f.value
+
+    def _set_peers(self, ed, part, flags):
+        n = len(ed)
+        arr = lambda v: (ctypes.c_void_p * n)(*v)   # noqa: E731
+        _lib.check(self._L.gsb_tracker_stripe_set_peers(self.trk._h, n, arr(ed), arr(part), arr(flags) if flags else None),
+                   "tracker_stripe_set_peers")
+        self.fused = n > 0
+        self._graph = None
+
+    def fuse_with_local_ranks(self, ranks):
+        """Test aid: all ranks of the stripe are ``StripedTracker`` objects of THIS process on one device and one stream;
+        the kernels store into each other's buffers directly and stream order replaces the barrier kernels."""
+        bufs = [r._own_exchange_buffers() for r in ranks]
+        self._set_peers([b[0] for b in bufs], [b[1] for b in bufs], None)
+
+    def fuse(self, group=None):
+        """Switch to the fused exchange: raster_fwd / loss / raster_bwd store their results straight into every rank's
+        buffers over NVLink (CUDA IPC handles exchanged once through ``torch.distributed``), two barrier kernels per
+        iteration, NO collective call.  One process per GPU on one node."""
+        import torch.distributed as dist
+        if self.world == 1:
+            return
+        own = self._own_exchange_buffers()
+        handles = []
+        for ptr in own:
+            h = (ctypes.c_ubyte * 64)()
+            _lib.check(self._L.gsb_ipc_export(ctypes.c_void_p(ptr), h), "ipc_export")
+            handles.append(bytes(h))
+        gathered = [None] * self.world
+        dist.all_gather_object(gathered, handles, group=group)
+        tables = ([], [], [])
+        self._opened = []
+        for r, hs in enumerate(gathered):
+            for k in range(3):
+                if r == self.rank:
+                    tables[k].append(own[k])
+                else:
+                    out = ctypes.c_void_p()
+                    _lib.check(self._L.gsb_ipc_open((ctypes.c_ubyte * 64).from_buffer_copy(hs[k]), ctypes.byref(out)), "ipc_open")
+                    self._opened.append(out.value)
+                    tables[k].append(out.value)
+        self._set_peers(*tables)
+        dist.barrier(group=group)      # every rank has zeroed its flags before anybody's first barrier kernel runs
+
+    def unfuse(self):
+        self._set_peers([], [], None)
+        for ptr in getattr(self, "_opened", []):
+            self._L.gsb_ipc_close(ctypes.c_void_p(ptr))
+        self._opened = []
+
     def segment(self, k: int):
         _lib.check(self._L.gsb_tracker_stripe_segment(self.trk._h, int(k)), "tracker_stripe_segment")
 
     def _one_iteration(self):
+        exchange = self.world > 1 and not getattr(self, "fused", False)
         self.segment(0)
-        if self.world > 1:
+        if exchange:
             self._all_reduce(self.depth)
         self.segment(1)
-        if self.world > 1:
+        if exchange:
             self._all_reduce(self.partials)
         self.segment(2)
 

@@ -198,6 +198,20 @@ int gsb_tracker_set_stripe(gsb_tracker* t, int rank, int world);
 int gsb_tracker_stripe_segment(gsb_tracker* t, int segment);
 /* device pointers and element counts (float) of the two exchanged buffers */
 int gsb_tracker_stripe_buffers(gsb_tracker* t, void** render_depth, void** partials, int64_t* n_depth, int64_t* n_partials);
+/* FUSED exchange (the compute + collective kernels of this path): instead of zero-filling foreign tiles and all-reducing,
+ * raster_fwd stores every pixel of its own tiles straight into the depth image of EVERY rank, and the loss / raster
+ * backward kernels store their partials into every rank's partials buffer (peer stores over NVLink; nothing is summed, so
+ * the result is the same bits); a barrier kernel (arrival epochs in each rank's flag words, system-scope fences) follows the
+ * forward and the backward inside the iteration.  Set-up: each rank takes its three buffers with
+ * gsb_tracker_stripe_exchange_buffers, exports them (gsb_ipc_export: cudaIpcGetMemHandle, 64 bytes each), the ranks exchange
+ * the handles (any transport; stripe.py: torch.distributed.all_gather_object), open them (gsb_ipc_open) and hand the tables
+ * to gsb_tracker_stripe_set_peers: one pointer per rank, entry [rank] the own buffer.  flags == NULL: no barrier kernels
+ * (every rank of a test runs on one stream of one device).  n == 0 switches back to the all-reduce exchange. */
+int gsb_tracker_stripe_exchange_buffers(gsb_tracker* t, void** render_depth, void** partials, void** flags);
+int gsb_tracker_stripe_set_peers(gsb_tracker* t, int n, void* const* render_depth, void* const* partials, void* const* flags);
+int gsb_ipc_export(const void* device_ptr, void* handle64);
+int gsb_ipc_open(const void* handle64, void** device_ptr);
+int gsb_ipc_close(void* device_ptr);
 /* synchronise; *overflowed != 0: a tile bin filled up (the iterations since are invalid: set the poses again);
  * *all_stopped: every camera's early stop has fired */
 int gsb_tracker_stripe_finish(gsb_tracker* t, int* overflowed, int* all_stopped);

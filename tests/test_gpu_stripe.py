@@ -94,6 +94,47 @@ def test_striped_ranks_reproduce_the_single_gpu_trajectory_bit_for_bit(gsb, worl
     ref.close()
 
 
+def test_fused_exchange_reproduces_the_single_gpu_trajectory_bit_for_bit(gsb):
+    """The fused exchange (kernels store their own tiles' pixels / partials into EVERY rank's buffers, no all-reduce): four
+    emulated ranks on one device and one stream (stream order stands in for the barrier kernels, which need one GPU per
+    rank: tools/stripe_parity.py --fused under torchrun)."""
+    from gsplatloc_b200.stripe import StripedTracker
+    world, n = 4, 10
+    fp = U.frame(U.MID_CAM, stride=2, seed=17)
+    q0, t0 = U.offgrid_pose(fp, torch.float64)
+    c2w0 = orc.pose_to_c2w(q0, t0).numpy()
+    ref = _make(gsb, fp, c2w0, early_stop=False)
+    ref.run(n, poll_every=0, use_graph=False)
+    ref_state, ref_hist = ref.states()[0], ref.history(0)
+    stream = torch.cuda.Stream()
+    ranks = []
+    for r in range(world):
+        means, quats, scales, opac = U.map_tensors(fp, torch.float32, "cuda")
+        trk = gsb.PoseTracker(fp.W, fp.H, 1, gsb.TrackerConfig(early_stop=False), stream=stream)
+        trk.set_map(means, quats, scales, opac)
+        trk.set_observation(torch.as_tensor(fp.src_depth, dtype=torch.float32).cuda(), fp.K)
+        trk.set_poses(c2w0, fp.src_c2w)
+        ranks.append(StripedTracker(trk, r, world, all_reduce=lambda t: None))
+    for st in ranks:
+        st.fuse_with_local_ranks(ranks)
+        st.segment(-1)
+    with torch.cuda.stream(stream):
+        for _ in range(n):
+            for k in (0, 1, 2):
+                for st in ranks:
+                    st.segment(k)
+    for st in ranks:
+        st.finish()
+        s = st.trk.states()[0]
+        assert np.array_equal(s["q"], ref_state["q"]) and np.array_equal(s["t"], ref_state["t"]), (st.rank, s["q"], ref_state["q"])
+        assert np.array_equal(st.trk.history(0), ref_hist)
+    d, _ = ref.render()
+    assert torch.equal(ranks[2].depth.view(fp.H, fp.W), d[0])
+    for st in ranks:
+        st.trk.close()
+    ref.close()
+
+
 def test_stripe_argument_checks(gsb):
     from gsplatloc_b200.stripe import StripedTracker
     fp = U.frame(U.SMALL_CAM, stride=2, seed=1)

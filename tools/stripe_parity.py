@@ -17,6 +17,7 @@ from gsplatloc_b200.stripe import StripedTracker
 ap = argparse.ArgumentParser()
 ap.add_argument("--workload", default="tum77k")
 ap.add_argument("--iters", type=int, default=25)
+ap.add_argument("--fused", action="store_true", help="peer stores + barrier kernels instead of NCCL all-reduces")
 args = ap.parse_args()
 rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
 torch.cuda.set_device(local)
@@ -41,6 +42,8 @@ ref.run(args.iters, poll_every=0, use_graph=True)
 rs, rh = ref.states()[0], ref.history(0)
 trk = make()
 st = StripedTracker(trk, rank, world)
+if args.fused:
+    st.fuse()
 st.iterate(args.iters)
 st.finish()
 s, h = trk.states()[0], trk.history(0)
@@ -52,7 +55,7 @@ flag = torch.tensor([int(same), int(same_img)], device=dev)
 if world > 1:
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 if rank == 0:
-    print(json.dumps({"workload": args.workload, "world": world, "iters": args.iters, "trajectory_bit_identical_on_every_rank": bool(flag[0]),
+    print(json.dumps({"workload": args.workload, "world": world, "fused": args.fused, "iters": args.iters, "trajectory_bit_identical_on_every_rank": bool(flag[0]),
                       "summed_image_bit_identical": bool(flag[1]), "eT_m": float(s["eT"]), "own_isects": trk.counters()["n_isects"],
                       "all_isects": ref.counters()["n_isects"]}), flush=True)
 if world > 1:
