@@ -8,6 +8,16 @@
 #define GSB_ALPHA_MIN (1.f / 255.f)  // A.4 skip threshold
 #define GSB_ALPHA_MAX 0.999f         // A.4 alpha clamp
 #define GSB_T_STOP 1e-4f             // A.4 stop threshold
+// two constants of the absent gsplat fork that neighbouring versions set differently.  Defaults =
+// upstream gsplat 1.3.0.  B2: -DGSB_RADIUS_FLOOR=0.1f (Inria's rasteriser).  B1: -DGSB_CLAMP_ASYMMETRIC=1 (gsplat >= 1.4.0:
+// lim+ = (W - cx) / fx + 0.3 tan_x, lim- = cx / fx + 0.3 tan_x).  The oracle has the same switches (oracle/gsplat_oracle.py
+// VARIANT); what they move is measured in tests/test_oracle.py::test_exposure_to_the_uncertain_constants.
+#ifndef GSB_RADIUS_FLOOR
+#define GSB_RADIUS_FLOOR 0.01f
+#endif
+#ifndef GSB_CLAMP_ASYMMETRIC
+#define GSB_CLAMP_ASYMMETRIC 0
+#endif
 
 namespace gsb {
 
@@ -89,13 +99,19 @@ struct Proj {
 __device__ __forceinline__ void persp_project(const Cam& cam, const float* __restrict__ Sc, int W, int H,
                                               float eps2d, float radius_clip, Proj& p) {
     float x = p.px, y = p.py, z = p.pz;
-    float limx = 1.3f * (0.5f * W / cam.fx), limy = 1.3f * (0.5f * H / cam.fy);
+    const float tanx = 0.5f * W / cam.fx, tany = 0.5f * H / cam.fy;
+#if GSB_CLAMP_ASYMMETRIC
+    const float lxp = ((float)W - cam.cx) / cam.fx + 0.3f * tanx, lxn = cam.cx / cam.fx + 0.3f * tanx;
+    const float lyp = ((float)H - cam.cy) / cam.fy + 0.3f * tany, lyn = cam.cy / cam.fy + 0.3f * tany;
+#else
+    const float lxp = 1.3f * tanx, lxn = lxp, lyp = 1.3f * tany, lyn = lyp;
+#endif
     float rz = 1.f / z, rz2 = rz * rz;
     float xr = x * rz, yr = y * rz;
-    p.in_x = (xr <= limx) && (xr >= -limx);
-    p.in_y = (yr <= limy) && (yr >= -limy);
-    float tx = z * fminf(limx, fmaxf(-limx, xr));
-    float ty = z * fminf(limy, fmaxf(-limy, yr));
+    p.in_x = (xr <= lxp) && (xr >= -lxn);
+    p.in_y = (yr <= lyp) && (yr >= -lyn);
+    float tx = z * fminf(lxp, fmaxf(-lxn, xr));
+    float ty = z * fminf(lyp, fmaxf(-lyn, yr));
     float j00 = cam.fx * rz, j11 = cam.fy * rz, j02 = -cam.fx * tx * rz2, j12 = -cam.fy * ty * rz2;
     p.rz = rz; p.tx = tx; p.ty = ty; p.j00 = j00; p.j11 = j11; p.j02 = j02; p.j12 = j12;
     float c00 = j00 * j00 * Sc[0] + 2.f * j00 * j02 * Sc[2] + j02 * j02 * Sc[5];
@@ -110,7 +126,7 @@ __device__ __forceinline__ void persp_project(const Cam& cam, const float* __res
     float idet = 1.f / det;
     p.ca = c11 * idet; p.cb = -c01 * idet; p.cc = c00 * idet;
     float b = 0.5f * (c00 + c11);
-    float v1 = b + sqrtf(fmaxf(0.01f, b * b - det));
+    float v1 = b + sqrtf(fmaxf(GSB_RADIUS_FLOOR, b * b - det));
     float radius = ceilf(3.f * sqrtf(v1));
     if (radius <= radius_clip) return;
     if (p.mx + radius <= 0.f || p.mx - radius >= (float)W || p.my + radius <= 0.f || p.my - radius >= (float)H) return;

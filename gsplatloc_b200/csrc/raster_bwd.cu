@@ -82,7 +82,7 @@ struct LiftCtx {
     int W, H, N, cam_index;
     float eps2d;
     int iso;   // every Gaussian has sx == sy == sz: Sigma = s^2 I whatever the quaternion (tracker.cu map_iso_kernel)
-    float inv_fx, inv_fy, limx, limy;   // raster_bwd_quad_kernel's record-based lift
+    float inv_fx, inv_fy, lxp, lxn, lyp, lyn;   // raster_bwd_quad_kernel's record-based lift (A.2 frustum clamp limits)
 };
 
 // A.6 for one Gaussian: the six patch-summed numbers (v_xy, v_conic, v_depth) -> 12 pose-gradient numbers, accumulated
@@ -357,8 +357,8 @@ __device__ __forceinline__ void lift_iso_cam(const LiftCtx* __restrict__ ctx, fl
     rz = rz * (2.f - z * rz);                       // one Newton step: 1 ulp
     const float xr = (mx - ctx->cam.cx) * ctx->inv_fx, yr = (my - ctx->cam.cy) * ctx->inv_fy;   // x / z, y / z
     const float pcx = xr * z, pcy = yr * z;
-    const bool in_x = fabsf(xr) <= ctx->limx, in_y = fabsf(yr) <= ctx->limy;
-    const float tx = z * fminf(ctx->limx, fmaxf(-ctx->limx, xr)), ty = z * fminf(ctx->limy, fmaxf(-ctx->limy, yr));
+    const bool in_x = xr <= ctx->lxp && xr >= -ctx->lxn, in_y = yr <= ctx->lyp && yr >= -ctx->lyn;
+    const float tx = z * fminf(ctx->lxp, fmaxf(-ctx->lxn, xr)), ty = z * fminf(ctx->lyp, fmaxf(-ctx->lyn, yr));
     const float rz2 = rz * rz, rz3 = rz2 * rz;
     const float j00 = fx * rz, j11 = fy * rz, j02 = -fx * tx * rz2, j12 = -fy * ty * rz2;
     // conic = inverse(cov2d): v_cov = -Cinv V Cinv, V = [[va, vb/2], [vb/2, vc]]
@@ -423,7 +423,13 @@ __global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad_
         s_ctx.W = W; s_ctx.H = H; s_ctx.N = N; s_ctx.cam_index = cam; s_ctx.eps2d = eps2d;
         s_ctx.iso = iso_flag ? *iso_flag : 0;
         s_ctx.inv_fx = 1.f / s_ctx.cam.fx; s_ctx.inv_fy = 1.f / s_ctx.cam.fy;
-        s_ctx.limx = 1.3f * (0.5f * W / s_ctx.cam.fx); s_ctx.limy = 1.3f * (0.5f * H / s_ctx.cam.fy);
+        const float tanx = 0.5f * W / s_ctx.cam.fx, tany = 0.5f * H / s_ctx.cam.fy;
+#if GSB_CLAMP_ASYMMETRIC
+        s_ctx.lxp = ((float)W - s_ctx.cam.cx) / s_ctx.cam.fx + 0.3f * tanx; s_ctx.lxn = s_ctx.cam.cx / s_ctx.cam.fx + 0.3f * tanx;
+        s_ctx.lyp = ((float)H - s_ctx.cam.cy) / s_ctx.cam.fy + 0.3f * tany; s_ctx.lyn = s_ctx.cam.cy / s_ctx.cam.fy + 0.3f * tany;
+#else
+        s_ctx.lxp = s_ctx.lxn = 1.3f * tanx; s_ctx.lyp = s_ctx.lyn = 1.3f * tany;
+#endif
     }
 #pragma unroll
     for (int k = 0; k < 12; ++k) s_pose[k * GSB_BWD_THREADS + tid] = 0.f;   // this thread's own column

@@ -113,6 +113,12 @@ class StripedTracker:
             self._L.gsb_ipc_close(ctypes.c_void_p(ptr))
         self._opened = []
 
+    def close(self):
+        """Leave the fused exchange (unmap the peers' buffers) and close the tracker."""
+        if getattr(self, "fused", False) or getattr(self, "_opened", None):
+            self.unfuse()
+        self.trk.close()
+
     def segment(self, k: int):
         _lib.check(self._L.gsb_tracker_stripe_segment(self.trk._h, int(k)), "tracker_stripe_segment")
 

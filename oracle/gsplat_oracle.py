@@ -23,6 +23,7 @@ dtype: every function computes in the dtype of its inputs.  fp64 = gradient trut
 from __future__ import annotations
 
 import math
+import os
 
 import numpy as np
 import torch
@@ -48,6 +49,15 @@ def quat_to_rotmat(q: torch.Tensor) -> torch.Tensor:
         2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)], -1).reshape(q.shape[:-1] + (3, 3))
 
 
+# two constants of the absent gsplat fork that neighbouring versions set differently.  The defaults
+# are upstream 1.3.0's (what the kernels are built with); the alternatives exist so that the exposure is a NUMBER
+# (tests/test_oracle.py::test_exposure_to_the_uncertain_constants) -- the kernels have the same two switches at compile time
+# (csrc/common.cuh: -DGSB_RADIUS_FLOOR=0.1f, -DGSB_CLAMP_ASYMMETRIC=1; the environment variables below select the oracle's
+# side for a GPU run against such a build).
+VARIANT = {"radius_floor": float(os.environ.get("GSB_ORACLE_RADIUS_FLOOR", "0.01")),      # B2: Inria's rasteriser uses 0.1
+           "clamp": os.environ.get("GSB_ORACLE_CLAMP", "symmetric")}                      # B1: "asymmetric" from gsplat 1.4.0
+
+
 def project(means, quats, scales, viewmats, Ks, width, height, eps2d=0.3, near_plane=0.01, far_plane=1e10,
             radius_clip=0.0):
     """-> radii[C,N] int32, means2d[C,N,2], depths[C,N], conics[C,N,3]; culled entries are zero."""
@@ -60,10 +70,16 @@ def project(means, quats, scales, viewmats, Ks, width, height, eps2d=0.3, near_p
     covc = torch.einsum("cij,njk,clk->cnil", R, cov, R)
     fx, fy, cx, cy = Ks[:, 0, 0, None], Ks[:, 1, 1, None], Ks[:, 0, 2, None], Ks[:, 1, 2, None]
     x, y, z = pc.unbind(-1)
-    limx, limy = 1.3 * (0.5 * width / fx), 1.3 * (0.5 * height / fy)
+    tanx, tany = 0.5 * width / fx, 0.5 * height / fy
+    if VARIANT["clamp"] == "asymmetric":   # gsplat >= 1.4.0
+        lxp, lxn = (width - cx) / fx + 0.3 * tanx, cx / fx + 0.3 * tanx
+        lyp, lyn = (height - cy) / fy + 0.3 * tany, cy / fy + 0.3 * tany
+    else:
+        lxp = lxn = 1.3 * tanx
+        lyp = lyn = 1.3 * tany
     rz = 1.0 / z
-    tx = z * torch.minimum(limx, torch.maximum(-limx, x * rz))
-    ty = z * torch.minimum(limy, torch.maximum(-limy, y * rz))
+    tx = z * torch.minimum(lxp, torch.maximum(-lxn, x * rz))
+    ty = z * torch.minimum(lyp, torch.maximum(-lyn, y * rz))
     O = torch.zeros_like(z)
     J = torch.stack([fx * rz, O, -fx * tx * rz * rz, O, fy * rz, -fy * ty * rz * rz], -1).reshape(C, N, 2, 3)
     cov2 = J @ covc @ J.transpose(-1, -2)
@@ -72,7 +88,7 @@ def project(means, quats, scales, viewmats, Ks, width, height, eps2d=0.3, near_p
     det = a * c - b * b
     conics = torch.stack([c / det, -b / det, a / det], -1)
     bb = 0.5 * (a + c)
-    v1 = bb + torch.sqrt(torch.clamp(bb * bb - det, min=0.01))
+    v1 = bb + torch.sqrt(torch.clamp(bb * bb - det, min=VARIANT["radius_floor"]))
     radius = torch.ceil(3.0 * torch.sqrt(v1))
     valid = (z >= near_plane) & (z <= far_plane) & (det > 0) & (radius > radius_clip)
     valid &= (m2[..., 0] + radius > 0) & (m2[..., 0] - radius < width)

@@ -109,3 +109,54 @@ def test_pose_loop_converges_to_the_known_delta():
     # the loss floor is set by the coarse splats of a 160x96 frame, so ask for a clear drop, not for zero
     assert res["history"][-1][0] < 0.9 * res["history"][0][0], "loss must drop"
     assert eT < 0.4 * eT0 and eR < 0.4 * eR0, (eT0, eT, eR0, eR)
+
+
+def test_exposure_to_the_uncertain_constants():
+    """the rasteriser's oracle restates gsplat 1.3.0 and cannot be pinned to
+    the absent fork, so the two constants that neighbouring versions set differently are switches (oracle VARIANT, kernels
+    -DGSB_RADIUS_FLOOR / -DGSB_CLAMP_ASYMMETRIC) and their effect on the synthetic frames is measured here:
+      B2 radius floor 0.01 -> 0.1 (Inria): GsplatLoc's maps are isotropic, so b^2 - det sits under either floor for every
+         Gaussian and v1 moves by sqrt(0.1) - sqrt(0.01) = 0.216 px^2: the 3-sigma radius of a few per cent of the Gaussians
+         crosses an integer, their tile lists grow, pixels at the rim (alpha between 1/255 and exp(-4.5)) change;
+      B1 asymmetric frustum clamp (gsplat >= 1.4.0): differs only for Gaussians whose centre projects more than 30 % outside
+         the image -- none on these frames."""
+    fp = U.frame(U.MID_CAM, stride=2, seed=3)
+    dt = torch.float64
+    means, quats, scales, opac = U.map_tensors(fp, dt)
+    gt, K = torch.tensor(fp.src_depth, dtype=dt), torch.tensor(fp.K, dtype=dt)
+    q0, t0 = U.offgrid_pose(fp, dt)
+
+    def run():
+        q, t = q0.clone().requires_grad_(True), t0.clone().requires_grad_(True)
+        tot, Ld, Ls, Ln, d, a, meta = orc.pose_loss(q, t, means, quats, scales, opac, gt, K, fp.W, fp.H)
+        tot.backward()
+        return dict(loss=float(tot), d=d.detach().numpy(), a=a.detach().numpy(), radii=meta["radii"].numpy(),
+                    M=int(meta["flatten_ids"].size), gq=q.grad.numpy(), gt=t.grad.numpy())
+
+    saved = dict(orc.VARIANT)
+    try:
+        base = run()
+        orc.VARIANT["radius_floor"] = 0.1
+        b2 = run()
+        orc.VARIANT.update(saved)
+        orc.VARIANT["clamp"] = "asymmetric"
+        b1 = run()
+    finally:
+        orc.VARIANT.update(saved)
+    vis = base["radii"] > 0
+    moved = float((b2["radii"][vis] != base["radii"][vis]).mean())
+    exposure = {"B2_gaussians_with_another_radius": moved, "B2_isects": (base["M"], b2["M"]),
+                "B2_depth_rel": U.rel_err(b2["d"], base["d"]), "B2_alpha_rel": U.rel_err(b2["a"], base["a"]),
+                "B2_loss_rel": abs(b2["loss"] - base["loss"]) / base["loss"],
+                "B2_grad_q_rel": U.rel_err(b2["gq"], base["gq"]), "B2_grad_t_rel": U.rel_err(b2["gt"], base["gt"]),
+                "B1_grad_rel": max(U.rel_err(b1["gq"], base["gq"]), U.rel_err(b1["gt"], base["gt"])),
+                "B1_isects": (base["M"], b1["M"])}
+    print(exposure)
+    # B1: no Gaussian of these frames is clamped -> nothing moves at all
+    assert b1["M"] == base["M"] and np.array_equal(b1["radii"], base["radii"]) and exposure["B1_grad_rel"] < 1e-12
+    # B2: a minority of radii grow by one pixel; the render and the pose gradient move by far less than the parity
+    # tolerances ask of the CUDA path (1e-4 / 1e-3) -- but not by nothing, which is why the constant is recorded
+    assert 0.0 < moved < 0.5 and b2["M"] >= base["M"]
+    assert np.all(b2["radii"][vis] - base["radii"][vis] >= 0) and np.all(b2["radii"][vis] - base["radii"][vis] <= 1)
+    assert exposure["B2_depth_rel"] < 1e-3 and exposure["B2_alpha_rel"] < 1e-3
+    assert exposure["B2_grad_q_rel"] < 2e-2 and exposure["B2_grad_t_rel"] < 2e-2
