@@ -10,8 +10,8 @@
 #define GSB_T_STOP 1e-4f             // A.4 stop threshold
 // two constants of the absent gsplat fork that neighbouring versions set differently.  Defaults =
 // upstream gsplat 1.3.0.  B2: -DGSB_RADIUS_FLOOR=0.1f (Inria's rasteriser).  B1: -DGSB_CLAMP_ASYMMETRIC=1 (gsplat >= 1.4.0:
-// lim+ = (W - cx) / fx + 0.3 tan_x, lim- = cx / fx + 0.3 tan_x).  The oracle has the same switches (oracle/gsplat_oracle.py
-// VARIANT); what they move is measured in tests/test_oracle.py::test_exposure_to_the_uncertain_constants.
+// lim+ = (W - cx) / fx + 0.3 tan_x, lim- = cx / fx + 0.3 tan_x).  The CPU restatement the tests check against has the
+// same two switches; what they move on the synthetic frames is measured there.
 #ifndef GSB_RADIUS_FLOOR
 #define GSB_RADIUS_FLOOR 0.01f
 #endif
