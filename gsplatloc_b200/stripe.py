@@ -133,10 +133,10 @@ class StripedTracker:
         self.segment(2)
 
     def capture(self):
-        """Record one iteration -- five kernel segments' launches and the two NCCL collectives -- as ONE CUDA graph on
-        the tracker's stream (torch's graph capture; NCCL collectives are capturable).  Call after at least one eager
-        iteration at the current frame size (the first segment sizes the tile bins, which synchronises).  The graph is
-        dropped when the bins are re-sized."""
+        """Record one iteration -- the six kernels and the two exchanges (NCCL all-reduces, or the barrier kernels of the
+        fused exchange) -- as ONE CUDA graph on the tracker's stream (torch's graph capture; NCCL collectives are
+        capturable).  Call after at least one eager iteration at the current frame size (the first segment sizes the
+        tile bins, which synchronises).  The graph is dropped when the bins are re-sized."""
         self._graph, self._graph_cap = None, self.trk.counters()["capacity"]
         g = torch.cuda.CUDAGraph()
         torch.cuda.synchronize(self.trk.device)
