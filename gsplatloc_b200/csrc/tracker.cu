@@ -49,6 +49,8 @@ struct gsb_tracker {
     unsigned char* masks = nullptr;   // per tile entry: which 8x4 patches it can reach (written by raster_fwd)
     int2* ranges = nullptr;           // per (camera, tile): [start, end) of its sorted entries (fixed-capacity bins)
     int tile_cap = 0;                 // keys per bin
+    int sized_N = 0;                  // map size the bins were last sized for (0: count again)
+    int grow_to = 0;                  // a striped run overflowed: the next sizing gives at least this many keys per bin
     int64_t cap = 0;                  // total = C * tiles * tile_cap
     float *ed = nullptr, *alpha = nullptr, *v_depth = nullptr, *v_alpha = nullptr;
     int* last_ids = nullptr;
@@ -57,6 +59,8 @@ struct gsb_tracker {
     float* history = nullptr;
     int history_cap = 0;
     int* h_flags = nullptr;  // pinned: [C] stop flags, then n_isects, overflow
+    void* h_stage = nullptr;          // pinned staging of set_poses / set_observation (no stream sync: guarded by stage_ev)
+    cudaEvent_t stage_ev = nullptr;
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
     bool graph_valid = false, have_map = false, have_obs = false, have_pose = false, cap_dirty = true;
@@ -214,6 +218,14 @@ static int ensure_capacity(gsb_tracker* t) {
     cudaStream_t st = t->stream;
     const gsb_tracker_config& c = t->cfg;
     launch_pose_begin(t->C, t->state, t->viewmats, st);
+    if (t->tile_cap > 0 && t->sized_N == t->N && t->grow_to == 0) {
+        // new poses (or the next frame of a sequence: a map of the same size) on bins that are already sized: no counting
+        // pass, no host synchronisation.  Capacity only ever grows, and a bin that fills up after all is caught by the
+        // overflow flag (gsb_tracker_run restores the poses, re-sizes and repeats, bit-identically).
+        t->total_launches += 1;
+        t->cap_dirty = false;
+        return GSB_OK;
+    }
     launch_project_bin(t->C, t->N, t->means, t->quats, t->scales, t->opac, t->viewmats, t->Ks, t->W, t->H, t->tile_w,
                        t->tile_h, c.eps2d, c.near_plane, c.far_plane, c.radius_clip, t->rec, t->bbox, t->counts,
                        t->stop, st);
@@ -229,7 +241,9 @@ static int ensure_capacity(gsb_tracker* t) {
     // bins are sized for the fullest tile + 50 % + 64; a bin that still fills up during a run (the view moves by tiles
     // between the start pose and the optimum) is caught by the overflow flag: gsb_tracker_run restores the poses,
     // doubles the bins and repeats
-    const int want_cap = ((fullest + fullest / 2 + 64) + 31) & ~31;
+    const int want_cap = std::max(((fullest + fullest / 2 + 64) + 31) & ~31, t->grow_to);
+    t->grow_to = 0;
+    t->sized_N = t->N;
     if (want_cap > t->tile_cap || t->tile_cap == 0) {
         int rc = resize_bins(t, want_cap);
         if (rc) return rc;
@@ -316,6 +330,8 @@ static int tracker_alloc(gsb_tracker* t, int C, int W, int H, void* stream) {
     TCK(cudaMalloc(&t->normal_rows, sizeof(float) * (size_t)C * H * 9), "alloc");
     TCK(cudaMalloc(&t->history, sizeof(float) * (size_t)t->history_cap * C * 8), "alloc");
     TCK(cudaMallocHost(&t->h_flags, sizeof(int) * (C + 2)), "alloc pinned");
+    TCK(cudaMallocHost(&t->h_stage, std::max(sizeof(gsb_pose_state), sizeof(float) * 9) * (size_t)C), "alloc pinned");
+    TCK(cudaEventCreateWithFlags(&t->stage_ev, cudaEventDisableTiming), "event");
     TCK(cudaMemsetAsync(t->counts, 0, sizeof(int) * nb, t->stream), "memset");
     TCK(cudaMemsetAsync(t->stop, 0, sizeof(int) * C, t->stream), "memset");
     TCK(cudaMemsetAsync(t->n_isects, 0, sizeof(int) * 3, t->stream), "memset");
@@ -356,6 +372,8 @@ void gsb_tracker_destroy(gsb_tracker* t) {
     for (void* b : bufs)
         if (b) cudaFree(b);
     if (t->h_flags) cudaFreeHost(t->h_flags);
+    if (t->h_stage) cudaFreeHost(t->h_stage);
+    if (t->stage_ev) cudaEventDestroy(t->stage_ev);
     if (t->ev0) cudaEventDestroy(t->ev0);
     if (t->ev1) cudaEventDestroy(t->ev1);
     if (t->own_stream) cudaStreamDestroy(t->stream);
@@ -367,6 +385,7 @@ int gsb_tracker_set_config(gsb_tracker* t, const gsb_tracker_config* cfg) {
     t->cfg = *cfg;
     invalidate_graph(t);  // the config is baked into kernel arguments
     t->cap_dirty = true;
+    t->sized_N = 0;       // near / far plane, eps2d, radius clip change what lands in the bins: count again
     return GSB_OK;
 }
 
@@ -405,17 +424,19 @@ int gsb_tracker_set_observation(gsb_tracker* t, const float* depth, int on_host,
     TCK(cudaMemcpyAsync(t->gt, depth, sizeof(float) * (size_t)t->W * t->H,
                         on_host ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, t->stream), "copy depth");
     launch_edge_magnitude(t->W, t->H, t->gt, t->gt_edge, t->stream);
-    std::vector<float> ks((size_t)t->C * 9);
-    for (int c = 0; c < t->C; ++c) memcpy(ks.data() + c * 9, K_host, sizeof(float) * 9);
-    TCK(cudaMemcpyAsync(t->Ks, ks.data(), sizeof(float) * ks.size(), cudaMemcpyHostToDevice, t->stream), "copy K");
-    TCK(cudaStreamSynchronize(t->stream), "sync");  // ks is a temporary
+    TCK(cudaEventSynchronize(t->stage_ev), "staging");   // the previous copy out of the pinned staging buffer is done
+    float* ks = static_cast<float*>(t->h_stage);
+    for (int c = 0; c < t->C; ++c) memcpy(ks + c * 9, K_host, sizeof(float) * 9);
+    TCK(cudaMemcpyAsync(t->Ks, ks, sizeof(float) * 9 * (size_t)t->C, cudaMemcpyHostToDevice, t->stream), "copy K");
+    TCK(cudaEventRecord(t->stage_ev, t->stream), "staging");
     t->have_obs = true;
     return GSB_OK;
 }
 
 int gsb_tracker_set_poses(gsb_tracker* t, const float* c2w_init_host, const float* c2w_gt_host) {
     if (!t || !c2w_init_host) return fail(GSB_ERR_ARG, "gsb_tracker_set_poses: null", cudaSuccess);
-    std::vector<gsb_pose_state> st((size_t)t->C);
+    TCK(cudaEventSynchronize(t->stage_ev), "staging");   // the previous copy out of the pinned staging buffer is done
+    gsb_pose_state* st = static_cast<gsb_pose_state*>(t->h_stage);
     for (int c = 0; c < t->C; ++c) {
         gsb_pose_state& s = st[c];
         memset(&s, 0, sizeof s);
@@ -430,10 +451,10 @@ int gsb_tracker_set_poses(gsb_tracker* t, const float* c2w_init_host, const floa
             memcpy(s.gt_c2w, c2w_gt_host + c * 16, sizeof(float) * 12);
         }
     }
-    TCK(cudaMemcpyAsync(t->state, st.data(), sizeof(gsb_pose_state) * st.size(), cudaMemcpyHostToDevice, t->stream), "copy state");
+    TCK(cudaMemcpyAsync(t->state, st, sizeof(gsb_pose_state) * (size_t)t->C, cudaMemcpyHostToDevice, t->stream), "copy state");
+    TCK(cudaEventRecord(t->stage_ev, t->stream), "staging");
     TCK(cudaMemsetAsync(t->stop, 0, sizeof(int) * t->C, t->stream), "memset stop");
     TCK(cudaMemsetAsync(t->overflow, 0, sizeof(int), t->stream), "memset overflow");
-    TCK(cudaStreamSynchronize(t->stream), "sync");
     t->have_pose = true; t->cap_dirty = true;
     return GSB_OK;
 }
@@ -501,6 +522,7 @@ int gsb_tracker_run(gsb_tracker* t, int n_iters, int poll_every, int use_graph, 
         }
         // at least the sizing rule at the restored poses, and at least twice what just proved too small
         const int failed_cap = t->tile_cap;
+        t->sized_N = 0;   // count again at the restored poses
         int rc = ensure_capacity(t);
         if (rc) return rc;
         if (t->tile_cap < 2 * failed_cap) {
@@ -545,7 +567,7 @@ int gsb_tracker_profile(gsb_tracker* t, int n_iters, float* stage_ms_host) {
     if (t->h_flags[t->C + 1]) {   // no restore / repeat here: the timings would be of invalid iterations
         cudaMemsetAsync(t->overflow, 0, sizeof(int), t->stream);
         cudaMemsetAsync(t->cursor, 0, sizeof(int) * (size_t)t->C * t->n_tiles, t->stream);
-        t->cap_dirty = true;
+        t->cap_dirty = true; t->sized_N = 0;
         return fail(GSB_ERR_OVERFLOW, "gsb_tracker_profile: a tile bin overflowed; set the poses again and repeat", cudaSuccess);
     }
     return GSB_OK;
@@ -568,7 +590,7 @@ int gsb_tracker_forward(gsb_tracker* t) {
     if (t->h_flags[t->C + 1]) {   // cannot happen after a sizing pass at these very poses; checked all the same
         cudaMemsetAsync(t->overflow, 0, sizeof(int), t->stream);
         cudaMemsetAsync(t->cursor, 0, sizeof(int) * (size_t)t->C * t->n_tiles, t->stream);
-        t->cap_dirty = true;
+        t->cap_dirty = true; t->sized_N = 0;
         return fail(GSB_ERR_OVERFLOW, "gsb_tracker_forward: a tile bin overflowed", cudaSuccess);
     }
     return GSB_OK;
@@ -726,6 +748,11 @@ int gsb_tracker_stripe_finish(gsb_tracker* t, int* overflowed, int* all_stopped)
     if (barrier_error)
         return fail(GSB_ERR_CUDA, "gsb_tracker_stripe_finish: a rank of the striped frame did not reach a barrier within 2 s", cudaSuccess);
     t->last_n_isects = t->h_flags[t->C];
+    if (t->h_flags[t->C + 1]) {   // the next sizing pass (after the caller's set_poses) counts again and at least doubles
+        cudaMemsetAsync(t->overflow, 0, sizeof(int), st);
+        cudaMemsetAsync(t->cursor, 0, sizeof(int) * (size_t)t->C * t->n_tiles, st);
+        t->grow_to = 2 * t->tile_cap; t->sized_N = 0; t->cap_dirty = true;
+    }
     if (overflowed) *overflowed = t->h_flags[t->C + 1] != 0;
     if (all_stopped) {
         *all_stopped = 1;

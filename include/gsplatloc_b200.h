@@ -225,8 +225,8 @@ int gsb_tracker_debug_copy(gsb_tracker* t, int32_t* flatten_ids, int32_t* offset
  * quotient), into caller-allocated DEVICE buffers (either may be NULL); parity-test aid */
 int gsb_tracker_debug_loss_grads(gsb_tracker* t, float* v_depth, float* v_alpha);
 /* test aid for the overflow path: shrink the per-tile bin capacity below what the sizing pass chose, so that the next
- * gsb_tracker_run fills a bin, raises the flag and returns GSB_ERR_OVERFLOW (the bins are re-sized by the next
- * gsb_tracker_set_poses + run). */
+ * gsb_tracker_run fills a bin, raises the flag, restores the poses, re-sizes and repeats (GSB_ERR_OVERFLOW only when the
+ * bins cannot be grown further). */
 int gsb_tracker_debug_limit_bins(gsb_tracker* t, int tile_cap);
 /* measurement aid: run n_iters iterations un-graphed with CUDA events between the kernels; stage_ms_host[9] gets
  * the mean device time of {pose_begin, project_bin, tile_scan, bin_emit, tile_sort, raster_fwd, loss, raster_bwd,
