@@ -577,23 +577,25 @@ int gsb_tracker_forward(gsb_tracker* t) {
     if (!t || !t->have_map || !t->have_pose)
         return fail(GSB_ERR_ARG, "gsb_tracker_forward: map and poses must be set first", cudaSuccess);
     if (!t->have_obs) return fail(GSB_ERR_ARG, "gsb_tracker_forward: intrinsics (set_observation) must be set first", cudaSuccess);
-    if (t->cap_dirty) {
-        int rc = ensure_capacity(t);
-        if (rc) return rc;
-    }
-    enqueue_iteration(t, true);
-    TCK(cudaMemcpyAsync(t->h_flags + t->C, t->n_isects, sizeof(int) * 2, cudaMemcpyDeviceToHost, t->stream), "flags");
-    TCK(cudaStreamSynchronize(t->stream), "forward sync");
-    TCK(cudaGetLastError(), "forward");
-    t->total_launches += 3;
-    t->last_n_isects = t->h_flags[t->C];
-    if (t->h_flags[t->C + 1]) {   // cannot happen after a sizing pass at these very poses; checked all the same
+    for (int attempt = 0;; ++attempt) {
+        if (t->cap_dirty) {
+            int rc = ensure_capacity(t);
+            if (rc) return rc;
+        }
+        enqueue_iteration(t, true);
+        TCK(cudaMemcpyAsync(t->h_flags + t->C, t->n_isects, sizeof(int) * 2, cudaMemcpyDeviceToHost, t->stream), "flags");
+        TCK(cudaStreamSynchronize(t->stream), "forward sync");
+        TCK(cudaGetLastError(), "forward");
+        t->total_launches += 3;
+        t->last_n_isects = t->h_flags[t->C];
+        if (!t->h_flags[t->C + 1]) return GSB_OK;
+        // bins that were sized for an earlier pose / frame of this map size filled up: count at these very poses (which
+        // cannot overflow) and render again; the forward changes no state, so there is nothing to restore
         cudaMemsetAsync(t->overflow, 0, sizeof(int), t->stream);
         cudaMemsetAsync(t->cursor, 0, sizeof(int) * (size_t)t->C * t->n_tiles, t->stream);
         t->cap_dirty = true; t->sized_N = 0;
-        return fail(GSB_ERR_OVERFLOW, "gsb_tracker_forward: a tile bin overflowed", cudaSuccess);
+        if (attempt >= 1) return fail(GSB_ERR_OVERFLOW, "gsb_tracker_forward: a tile bin overflowed", cudaSuccess);
     }
-    return GSB_OK;
 }
 
 int gsb_tracker_get_states(gsb_tracker* t, gsb_pose_state* out_host) {

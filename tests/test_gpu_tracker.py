@@ -401,3 +401,35 @@ def test_chained_walk_tracks_three_frames(gsb, chain):
     assert res.records.shape[0] == 3 and res.iters > 300
     assert eT.max() < 3e-3, eT                         # error against the ABSOLUTE ground truth: accumulated drift
     trk.close()
+
+
+def test_bins_sized_for_another_pose_are_regrown_without_a_counting_pass(gsb):
+    """Once the bins are sized for a map size, new poses (and the next frame of a sequence) skip the counting pass and its
+    host synchronisation; bins that then prove too small are caught by the overflow flag -- ``forward`` recounts and
+    renders again, ``run`` restores / re-sizes / repeats -- and the results are those of a freshly sized tracker."""
+    fp = U.frame(U.SMALL_CAM, stride=2, seed=42)
+    c2w0 = _start_pose(fp)
+    far = c2w0.copy()
+    far[:3, 3] -= 6.0 * far[:3, 2]            # six metres back along the optical axis: every Gaussian lands in a few tiles... or none
+    fresh = _tracker(gsb, fp, c2w0, fp.src_depth, early_stop=False)
+    fresh.forward()
+    d_ref, a_ref = fresh.render()
+    fresh.run(12, poll_every=0)
+    want = fresh.states()[0]
+    fresh.close()
+
+    trk = _tracker(gsb, fp, far, fp.src_depth, early_stop=False)
+    trk.forward()                             # sizes the bins at the far pose
+    trk.set_poses(c2w0, fp.src_c2w)           # no counting pass now
+    trk.forward()
+    d, a = trk.render()
+    assert torch.equal(d, d_ref) and torch.equal(a, a_ref)
+    trk.set_poses(far, fp.src_c2w); trk.forward()
+    trk.debug_limit_bins(8)                   # and the loop: bins far too small for the near pose
+    trk.set_poses(c2w0, fp.src_c2w)
+    trk.run(12, poll_every=0)
+    got = trk.states()[0]
+    assert np.array_equal(got["q"], want["q"]) and np.array_equal(got["t"], want["t"]) and got["loss"] == want["loss"]
+    tiles = math.ceil(fp.W / 16) * math.ceil(fp.H / 16)
+    assert trk.counters()["capacity"] > 8 * tiles      # the limited bins were re-sized by the repeat
+    trk.close()
