@@ -147,3 +147,63 @@ def test_stripe_argument_checks(gsb):
     one.run(3, poll_every=0)
     assert trk.states()[0]["iter"] == 3
     trk.close()
+
+
+@pytest.mark.parametrize("fused", [False, True])
+def test_two_hypotheses_and_the_early_stop_on_striped_ranks(gsb, fused):
+    """C = 2 pose hypotheses of the striped frame with the early stop on (short patience so that it fires inside the run):
+    every emulated rank must stop both cameras in the iteration the unstriped tracker stops them and hold the same states."""
+    from gsplatloc_b200.stripe import StripedTracker
+    world, n = 2, 40
+    fp = U.frame(U.SMALL_CAM, stride=2, seed=23, trans_cm=1.0, rot_deg=0.5)
+    p0 = fp.tar_c2w.astype(np.float64)
+    p1 = p0.copy(); p1[:3, 3] += np.array([0.004, -0.003, 0.002])
+    poses = np.stack([p0, p1])
+    cfg = dict(early_stop=True, patience=4, warmup=3, max_steps=200, trans_lr=0.02, quat_lr=0.01)   # steps far too large: the loss bounces
+
+    def make(stream=None):
+        means, quats, scales, opac = U.map_tensors(fp, torch.float32, "cuda")
+        trk = gsb.PoseTracker(fp.W, fp.H, 2, gsb.TrackerConfig(**cfg), stream=stream)
+        trk.set_map(means, quats, scales, opac)
+        trk.set_observation(torch.as_tensor(fp.src_depth, dtype=torch.float32).cuda(), fp.K)
+        trk.set_poses(poses, fp.src_c2w)
+        return trk
+
+    ref = make()
+    ref.run(n, poll_every=0, use_graph=False)
+    want = ref.states()
+    assert any(s["stopped"] for s in want), "the early stop must fire inside the run for the test to mean something"
+    stream = torch.cuda.Stream()
+    ranks = [StripedTracker(make(stream), r, world, all_reduce=lambda t: None) for r in range(world)]
+    if fused:
+        for st in ranks:
+            st.fuse_with_local_ranks(ranks)
+    for st in ranks:
+        st.segment(-1)
+
+    def summed(kind):
+        total = torch.stack([getattr(r, kind) for r in ranks]).sum(0)
+        for r in ranks:
+            getattr(r, kind).copy_(total)
+
+    with torch.cuda.stream(stream):
+        for _ in range(n):
+            for st in ranks:
+                st.segment(0)
+            if not fused:
+                summed("depth")
+            for st in ranks:
+                st.segment(1)
+            if not fused:
+                summed("partials")
+            for st in ranks:
+                st.segment(2)
+    for st in ranks:
+        st.finish()
+        got = st.trk.states()
+        for c in range(2):
+            assert got[c]["stopped"] == want[c]["stopped"] and got[c]["iter"] == want[c]["iter"], (st.rank, c)
+            assert np.array_equal(got[c]["q"], want[c]["q"]) and np.array_equal(got[c]["t"], want[c]["t"])
+            assert got[c]["best_iter"] == want[c]["best_iter"] and got[c]["best_eT"] == want[c]["best_eT"]
+        st.trk.close()
+    ref.close()
