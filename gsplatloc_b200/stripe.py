@@ -27,6 +27,20 @@ from . import _lib
 from .tracker import PoseTracker
 
 
+def tile_owner(tx, ty, tile_w: int, world: int):
+    """Rank that owns raster tile (tx, ty) of a striped frame: host mirror of ``stripe_owns`` (csrc/common.cuh).  Horizontal
+    tile pairs (32x16 pixels = four 32x8 loss blocks), interleaved over the ranks; ``world`` a power of two.  Works on ints
+    and on numpy arrays."""
+    if world & (world - 1):
+        raise ValueError("world must be a power of two")
+    return (ty * ((tile_w + 1) >> 1) + (tx >> 1)) & (world - 1)
+
+
+def loss_block_owner(bx, by, tile_w: int, world: int):
+    """Rank that evaluates the 32x8 loss block (bx, by): the owner of the tile pair it lies in."""
+    return tile_owner(2 * bx, by >> 1, tile_w, world)
+
+
 class _DevArray:
     """Zero-copy view of a raw device pointer for ``torch.as_tensor`` (CUDA array interface, float32)."""
 

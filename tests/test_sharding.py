@@ -77,3 +77,31 @@ def test_gather_records_single_process_is_identity_sorted():
     rows = [sh.state_to_record(f, 0, _fake_state(f)) for f in (3, 1, 2)]
     r = sh.gather_records(rows)
     assert list(r[:, 0]) == [1, 2, 3]
+
+
+def test_stripe_ownership_partitions_tiles_and_loss_blocks():
+    """Row f3 host logic (no GPU): every tile has one owner, the two tiles of a horizontal pair share it, the four 32x8
+    loss blocks inside a pair belong to the same rank, and the interleaving balances the ranks to within a few pairs --
+    for the three benchmark shapes (75x43 tiles with an odd width, 40x30, 120x68) and world sizes 1 ... 8."""
+    import numpy as np
+    pytest = __import__("pytest")
+    # the CUDA library is not needed for the partition functions, but the module imports the tracker: skip if it cannot
+    stripe = pytest.importorskip("gsplatloc_b200.stripe")
+    for W, H in ((1200, 680), (640, 480), (1920, 1080)):
+        tw, th = (W + 15) // 16, (H + 15) // 16
+        tx, ty = np.meshgrid(np.arange(tw), np.arange(th))
+        for world in (1, 2, 4, 8):
+            own = stripe.tile_owner(tx, ty, tw, world)
+            assert own.min() >= 0 and own.max() == world - 1
+            left = own[:, 0:tw - (tw % 2):2]
+            right = own[:, 1:tw:2]
+            assert np.array_equal(left[:, :right.shape[1]], right), "the tiles of a pair share their owner"
+            share = np.bincount(own.ravel(), minlength=world) / own.size
+            assert share.max() - share.min() < 0.02, (W, H, world, share)
+            # loss blocks: 32x8 pixels; block (bx, by) lies in tiles (2bx, by // 2) and (2bx + 1, by // 2)
+            gx, gy = (W + 31) // 32, (H + 7) // 8
+            bx, by = np.meshgrid(np.arange(gx), np.arange(gy))
+            lown = stripe.loss_block_owner(bx, by, tw, world)
+            assert np.array_equal(lown, own[np.minimum(by // 2, th - 1), np.minimum(2 * bx, tw - 1)])
+    with pytest.raises(ValueError):
+        stripe.tile_owner(0, 0, 10, 3)
