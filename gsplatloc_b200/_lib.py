@@ -56,6 +56,7 @@ _SIGS = {
     "gsb_sh_fwd": (c_i, [c_i, c_i, c_i, c_p, c_p, c_p, c_p, c_p]),
     "gsb_sh_bwd": (c_i, [c_i, c_i, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),
     "gsb_depth_edge_loss": (c_i, [c_i, c_i, c_i, c_p, c_p, c_i, c_i, c_f, c_f, c_p, c_p, c_p, c_p]),
+    "gsb_depth_edge_loss_static": (c_i, [c_i, c_i, c_i, c_p, c_p, c_i, c_i, c_f, c_f, c_p, c_p, c_p]),
     "gsb_loss_workspace_floats": (c_sz, [c_i, c_i, c_i]),
     "gsb_depth_edge_normal_loss": (c_i, [c_i, c_i, c_i, c_p, c_p, c_i, c_i, c_p, c_f, c_f, c_f, c_i, c_p, c_p, c_p,
                                          c_p]),

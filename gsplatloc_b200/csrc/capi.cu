@@ -2,6 +2,7 @@
 #include <math.h>
 #include <stdio.h>
 
+#include <mutex>
 #include <string>
 
 #include "common.cuh"
@@ -214,6 +215,57 @@ int gsb_depth_edge_loss(int C, int width, int height, const float* depth, const 
                 w_s, 0.f, 0, nullptr, nullptr, 0, v_depth, nullptr, partial_ws, nullptr, nullptr, Stripe(), st);
     reduce_loss_partials_kernel<<<C, 256, 0, st>>>(gx * gy, partial_ws, loss_sums, 2);
     CK_LAUNCH("gsb_depth_edge_loss");
+    return GSB_OK;
+}
+
+// ---- the same loss with its block partials in a file-scope device array: nothing is allocated by the call.
+// g_static_loss_partials is a host-side stand-in in host code; its device address comes from cudaGetSymbolAddress,
+// looked up once per device (with that device current) and kept in g_static_loss_ptr.
+}  // extern "C"
+#define GSB_STATIC_LOSS_MAX_DEVICES 64
+static __device__ __align__(256) float g_static_loss_partials[3 * GSB_STATIC_LOSS_MAX_BLOCKS];
+static float* g_static_loss_ptr[GSB_STATIC_LOSS_MAX_DEVICES];
+static std::mutex g_static_loss_mutex;
+extern "C" {
+
+int gsb_depth_edge_loss_static(int C, int width, int height, const float* depth, const float* gt, int gt_per_camera,
+                               int apply_mask, float w_d, float w_s, float* loss_sums, float* v_depth, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (C <= 0 || width <= 0 || height <= 0)
+        return fail(GSB_ERR_ARG, "gsb_depth_edge_loss_static: bad sizes", cudaSuccess);
+    int gx, gy;
+    loss_grid(width, height, &gx, &gy);
+    const long long n_blocks = (long long)C * gx * gy;
+    if (n_blocks > GSB_STATIC_LOSS_MAX_BLOCKS) {
+        char msg[200];
+        snprintf(msg, sizeof msg, "gsb_depth_edge_loss_static: C*ceil(W/32)*ceil(H/8) = %lld loss blocks exceed the "
+                 "static scratch of %d (GSB_STATIC_LOSS_MAX_BLOCKS); use gsb_depth_edge_loss", n_blocks,
+                 GSB_STATIC_LOSS_MAX_BLOCKS);
+        return fail(GSB_ERR_ARG, msg, cudaSuccess);
+    }
+    if (!depth || !gt || !loss_sums || !v_depth)
+        return fail(GSB_ERR_ARG, "gsb_depth_edge_loss_static: null pointer", cudaSuccess);
+    int dev = -1;
+    CK(cudaGetDevice(&dev), "gsb_depth_edge_loss_static cudaGetDevice");
+    if (dev < 0 || dev >= GSB_STATIC_LOSS_MAX_DEVICES)
+        return fail(GSB_ERR_ARG, "gsb_depth_edge_loss_static: device ordinal beyond 63", cudaSuccess);
+    float* partials = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_static_loss_mutex);
+        if (!g_static_loss_ptr[dev]) {
+            void* p = nullptr;
+            CK(cudaGetSymbolAddress(&p, g_static_loss_partials), "gsb_depth_edge_loss_static cudaGetSymbolAddress");
+            if (!p) return fail(GSB_ERR_CUDA, "gsb_depth_edge_loss_static: null symbol address", cudaSuccess);
+            g_static_loss_ptr[dev] = (float*)p;
+        }
+        partials = g_static_loss_ptr[dev];
+    }
+    // the array keeps the previous call's partials: clear the slots this call reduces over
+    CK(cudaMemsetAsync(partials, 0, sizeof(float) * 3 * (size_t)n_blocks, st), "gsb_depth_edge_loss_static memset");
+    launch_loss(C, width, height, depth, nullptr, gt, gt_per_camera ? (size_t)width * height : 0, apply_mask, w_d,
+                w_s, 0.f, 0, nullptr, nullptr, 0, v_depth, nullptr, partials, nullptr, nullptr, Stripe(), st);
+    reduce_loss_partials_kernel<<<C, 256, 0, st>>>(gx * gy, partials, loss_sums, 2);
+    CK_LAUNCH("gsb_depth_edge_loss_static");
     return GSB_OK;
 }
 

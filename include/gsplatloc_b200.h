@@ -96,6 +96,21 @@ int gsb_depth_edge_loss(int C, int width, int height, const float* depth, const 
                         int apply_mask, float w_d, float w_s, float* loss_sums, float* v_depth, float* partial_ws,
                         void* stream);
 
+/* ---- gsb_depth_edge_loss without the caller's scratch buffer, for callers that cannot allocate (CUDA graph capture,
+ * serving loops, harnesses that forbid cudaMalloc).  This entry point has NO counterpart in the reference.
+ * Same arguments and results as gsb_depth_edge_loss minus partial_ws: the
+ * per-block partial sums live in a file-scope `static __device__` array of 3 * GSB_STATIC_LOSS_MAX_BLOCKS floats
+ * (384 KiB) that every GPU which loads the library holds until exit.  The call allocates nothing (no cudaMalloc /
+ * cudaFree, no allocating library routine) and launches a memset, the loss kernel and the reduction on `stream`.
+ * Limit: C * ceil(W/32) * ceil(H/8) <= GSB_STATIC_LOSS_MAX_BLOCKS (e.g. 1200x680 with C <= 10, 1920x1080 with C <= 4);
+ * larger sizes fail with GSB_ERR_ARG and a message naming the limit.
+ * All calls on one device share the array (it keeps the last call's partials; the used slots are cleared first), so two
+ * calls that overlap on the GPU - different streams, or the same graph launched twice concurrently - race on it:
+ * serialise them. */
+#define GSB_STATIC_LOSS_MAX_BLOCKS 32768
+int gsb_depth_edge_loss_static(int C, int width, int height, const float* depth, const float* gt, int gt_per_camera,
+                               int apply_mask, float w_d, float w_s, float* loss_sums, float* v_depth, void* stream);
+
 /* ---- the same plus compute_normal_consistency_loss (loss.py:62-101; depth_to_normal geometry.py:164-197,
  * depth_to_points :138-161 = kornia depth_to_3d_v2): normals n(D) = normalize(cross(dP/dx, dP/dy)) of the
  * back-projected, replicate-padded depth images, L_n = 1 - mean(cos(n(B), n(A))).
