@@ -355,9 +355,11 @@ __device__ void bitonic_sort(uint64_t* a, int n, bool smem) {
 //   otherwise    : one trip through shared memory (double-buffered: one block barrier per round).
 // For 512 slots that is 9 register rounds, 30 shuffle rounds and 6 shared-memory rounds instead of 45 shared-memory
 // rounds.  Stages whose lower half already holds every real key (2^(lh-1) >= n) are skipped: the rest is +inf.
+// Slots >= ``live_end`` belong to warps that hold nothing but +inf: those warps do not run the network (reg_tile_sort),
+// they only meet the block barriers of the shared-memory rounds, and their slots are read as +inf here.
 template <int K>
 __device__ __forceinline__ void reg_sort_round(uint64_t (&v)[K], int m, bool flip, int tid, int lane, uint64_t* sbuf,
-                                               int& parity) {
+                                               int& parity, int live_end) {
     constexpr int LGK = (K == 1) ? 0 : ((K == 2) ? 1 : ((K == 4) ? 2 : 3));
     if (m < K) {
 #pragma unroll
@@ -396,7 +398,7 @@ __device__ __forceinline__ void reg_sort_round(uint64_t (&v)[K], int m, bool fli
 #pragma unroll
     for (int e = 0; e < K; ++e) {
         const int i = K * tid + e, j = i ^ m;
-        const uint64_t recv = buf[j];
+        const uint64_t recv = (j < live_end) ? buf[j] : ~0ull;
         const bool lt = v[e] < recv;
         v[e] = (lt == (i < j)) ? v[e] : recv;
     }
@@ -412,13 +414,34 @@ __device__ __forceinline__ void reg_tile_sort(const uint64_t* __restrict__ g, in
 #pragma unroll
     for (int e = 0; e < K; ++e) v[e] = (K * tid + e < n) ? g[K * tid + e] : ~0ull;
     int parity = 0;
-    // fully unrolled: m, the lane offset and the min/max side of every round are immediates
+    // Warps whose slots are all >= n hold nothing but +inf, and +inf never moves in this network (a real key always sits
+    // at the lower index of its pair).  Such a warp skips the network and only meets the block barriers of the
+    // shared-memory rounds, one for one (the whole warp takes the same side, so every barrier instruction is executed by
+    // complete warps; the count per stage is the same on both sides).  With ~285-key bins in 512 slots that is three of
+    // the eight warps.  The flag comes from a vote so that the compiler knows it is warp-uniform.
+    constexpr int LGK = LGP - 8;
+    const int live_end = ((n + 32 * K - 1) / (32 * K)) * (32 * K);   // first slot of the first all-padding warp
+    const bool live = __any_sync(0xffffffffu, K * tid < n);
+    if (live) {
+        // fully unrolled: m, the lane offset and the min/max side of every round are immediates
 #pragma unroll
-    for (int lh = 1; lh <= LGP; ++lh) {
-        if ((1 << (lh - 1)) < n) {
-            reg_sort_round<K>(v, (1 << lh) - 1, true, tid, lane, sbuf, parity);
+        for (int lh = 1; lh <= LGP; ++lh) {
+            if ((1 << (lh - 1)) < n) {
+                reg_sort_round<K>(v, (1 << lh) - 1, true, tid, lane, sbuf, parity, live_end);
 #pragma unroll
-            for (int ld = lh - 2; ld >= 0; --ld) reg_sort_round<K>(v, 1 << ld, false, tid, lane, sbuf, parity);
+                for (int ld = lh - 2; ld >= 0; --ld)
+                    reg_sort_round<K>(v, 1 << ld, false, tid, lane, sbuf, parity, live_end);
+            }
+        }
+    } else {
+#pragma unroll
+        for (int lh = 1; lh <= LGP; ++lh) {
+            if ((1 << (lh - 1)) < n) {
+                if ((((1 << lh) - 1) >> LGK) >= 32) __syncthreads();
+#pragma unroll
+                for (int ld = lh - 2; ld >= 0; --ld)
+                    if (((1 << ld) >> LGK) >= 32) __syncthreads();
+            }
         }
     }
 #pragma unroll
