@@ -272,6 +272,11 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
+// Programmatic dependent launch (kernels.h launch_chain_kernel): wait for the predecessor kernel of the chain (complete,
+// writes visible); let the successor's blocks be scheduled behind this grid's.  No-ops in a plain launch.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // Tile-striped single frame over several GPUs: rank r owns the horizontal tile PAIRS (32x16 pixels:
 // four 32x8 loss blocks) whose index ty * ceil(tile_w / 2) + (tx >> 1) is r modulo the world size (a power of two;
 // stripe_mask = world - 1; 0 = one GPU owns everything).  Interleaved pairs balance the load, and a pair is the unit at

@@ -493,6 +493,8 @@ __global__ void __launch_bounds__(256) tile_sort_fixed_kernel(int n_tiles, int t
                                                               int* __restrict__ n_isects,
                                                               const int* __restrict__ stop) {
     __shared__ uint64_t sk[SORT_SMEM];
+    pdl_wait();
+    pdl_launch_dependents();
     const int bin = blockIdx.x;
     const int cam = bin / n_tiles;
     if (stop && stop[cam]) return;
@@ -531,8 +533,8 @@ __global__ void __launch_bounds__(256) compact_bins_kernel(const int2* __restric
 void launch_tile_sort_fixed(int C, int n_tiles, int tile_cap, int* cursor, uint64_t* keys, int* flatten_ids,
                             int2* ranges, int* n_isects, const int* stop, cudaStream_t st) {
     if (C * n_tiles == 0) return;
-    tile_sort_fixed_kernel<<<C * n_tiles, 256, 0, st>>>(n_tiles, tile_cap, cursor, keys, flatten_ids, ranges, n_isects,
-                                                        stop);
+    launch_chain_kernel(tile_sort_fixed_kernel, dim3(C * n_tiles), dim3(256), st, n_tiles, tile_cap, cursor, keys,
+                        flatten_ids, ranges, n_isects, stop);
 }
 
 void launch_compact_bins(int n_bins, const int2* ranges, const int* padded, const int* offsets, int* out,

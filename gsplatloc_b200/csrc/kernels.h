@@ -18,6 +18,24 @@ struct Stripe {
                                     // array with a run-time index would push the kernel parameters onto the local stack)
 };
 
+// Programmatic dependent launch for the tracker's kernel chain.  While g_pdl is set (tracker.cu: one GPU per frame, no
+// stage marks) the six kernels of an iteration are launched with the programmatic-stream-serialization attribute: a
+// kernel's blocks may be scheduled while its predecessor drains; every block executes pdl_wait() (common.cuh:
+// griddepcontrol.wait -- the predecessor has completed and its writes are visible) before it touches global memory or
+// exits, so the chain stays transitively ordered, and pdl_launch_dependents() right after lets the successor queue up.
+// Without the attribute both instructions do nothing.
+extern thread_local bool g_pdl;
+template <typename... KArgs, typename... Args>
+inline void launch_chain_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = 0; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = g_pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 // ---- projection.cu
 void launch_project_fwd(int C, int N, const float* means, const float* quats, const float* scales,
                         const float* viewmats, const float* Ks, int W, int H, float eps2d, float near_plane,

@@ -357,6 +357,8 @@ __global__ void __launch_bounds__(LBX* LBY) loss_track_kernel(
     __shared__ float sA[LH * LW], sB[LH * LW];
     __shared__ float sKx[(LBY + 2) * (LBX + 2)], sKy[(LBY + 2) * (LBX + 2)];
     __shared__ float s_red[2][(LBX * LBY) / 32];
+    pdl_wait();
+    pdl_launch_dependents();
     const int cam = blockIdx.z;
     if (stop && stop[cam]) return;
     const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * LBX + tx;
@@ -529,8 +531,8 @@ void launch_loss(int C, int W, int H, const float* ed, const float* alpha, const
         (long long)C * W * H < (1ll << 31)) {   // the tracker's configuration: the lean kernel
         // (fused stripe exchange: stripe.peer[r] is rank r's pose-partials buffer, which the loss partials follow)
         const size_t peer_offset = stripe.n_peers ? stripe_loss_offset : 0;
-        loss_track_kernel<<<grid, block, 0, st>>>(W, H, ed, alpha, gt, gt_edge, w_d, w_s, v_out, v_alpha, partial, stop,
-                                                  (W + GSB_TILE - 1) / GSB_TILE, stripe, peer_offset);
+        launch_chain_kernel(loss_track_kernel, grid, block, st, W, H, ed, alpha, gt, gt_edge, w_d, w_s, v_out, v_alpha,
+                            partial, stop, (W + GSB_TILE - 1) / GSB_TILE, stripe, peer_offset);
         return;
     }
     if (normal_mode == 2) {

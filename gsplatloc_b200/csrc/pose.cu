@@ -77,6 +77,8 @@ __global__ void __cluster_dims__(GSB_POSE_CLUSTER, 1, 1) __launch_bounds__(POSE_
     float* __restrict__ history, int history_cap) {
     __shared__ float red[15][POSE_FINISH_THREADS / 32];
     __shared__ float cred[GSB_POSE_CLUSTER][16];   // written by every block of the cluster into the LEADER's copy
+    pdl_wait();
+    pdl_launch_dependents();
     cg::cluster_group cluster = cg::this_cluster();
     const int rank = (int)cluster.block_rank();
     const int c = blockIdx.x / GSB_POSE_CLUSTER, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -230,8 +232,9 @@ void launch_pose_begin(int C, const gsb_pose_state* state, float* viewmats, cuda
 void launch_pose_finish(int C, int n_tiles, int n_loss_blocks, const float* partials, const float* loss_partials,
                         float* viewmats, gsb_pose_state* state, int* stop, gsb_tracker_config cfg,
                         float inv_pixels, float inv_rows3, float* history, int history_cap, cudaStream_t st) {
-    pose_finish_kernel<<<C * GSB_POSE_CLUSTER, POSE_FINISH_THREADS, 0, st>>>(C, n_tiles, n_loss_blocks, partials, loss_partials, viewmats, state, stop,
-                                          cfg, inv_pixels, inv_rows3, history, history_cap);
+    launch_chain_kernel(pose_finish_kernel, dim3(C * GSB_POSE_CLUSTER), dim3(POSE_FINISH_THREADS), st, C, n_tiles,
+                        n_loss_blocks, partials, loss_partials, viewmats, state, stop, cfg, inv_pixels, inv_rows3, history,
+                        history_cap);
 }
 
 }  // namespace gsb

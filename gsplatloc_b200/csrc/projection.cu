@@ -210,6 +210,8 @@ __global__ void __launch_bounds__(256) project_emit_kernel(
     // only into the tiles it owns (common.cuh stripe_owns; stripe_mask = world - 1, 0 = one GPU: every tile).  The
     // records are written for every Gaussian either way.
     __shared__ int s_incl[8][32];
+    pdl_wait();
+    pdl_launch_dependents();
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     const int c = blockIdx.y;
     if (n == 0 && c == 0) *n_isects = 0;
@@ -321,13 +323,13 @@ void launch_project_emit(int C, int N, const float* means, const float* quats, c
     if (N == 0 || C == 0) return;
     dim3 grid((N + 255) / 256, C);
     if (stripe_world > 1)
-        project_emit_kernel<true><<<grid, 256, 0, st>>>(C, N, means, quats, scales, opacities, viewmats, Ks, W, H, tile_w,
-                                                        tile_h, eps2d, near_plane, far_plane, radius_clip, rec, cursor, keys,
-                                                        tile_cap, n_isects, overflow, stop, stripe_rank, stripe_world - 1);
+        launch_chain_kernel(project_emit_kernel<true>, grid, dim3(256), st, C, N, means, quats, scales, opacities, viewmats,
+                            Ks, W, H, tile_w, tile_h, eps2d, near_plane, far_plane, radius_clip, rec, cursor, keys,
+                            tile_cap, n_isects, overflow, stop, stripe_rank, stripe_world - 1);
     else
-        project_emit_kernel<false><<<grid, 256, 0, st>>>(C, N, means, quats, scales, opacities, viewmats, Ks, W, H, tile_w,
-                                                         tile_h, eps2d, near_plane, far_plane, radius_clip, rec, cursor, keys,
-                                                         tile_cap, n_isects, overflow, stop, 0, 0);
+        launch_chain_kernel(project_emit_kernel<false>, grid, dim3(256), st, C, N, means, quats, scales, opacities, viewmats,
+                            Ks, W, H, tile_w, tile_h, eps2d, near_plane, far_plane, radius_clip, rec, cursor, keys,
+                            tile_cap, n_isects, overflow, stop, 0, 0);
 }
 
 void launch_project_bin(int C, int N, const float* means, const float* quats, const float* scales,

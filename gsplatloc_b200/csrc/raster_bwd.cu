@@ -396,6 +396,8 @@ __global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad_
     __shared__ float s_pose[12 * GSB_BWD_THREADS];
     __shared__ LiftCtx s_ctxs[GSB_BWD_WARPS];   // one copy per warp: no block barrier before the loop
 
+    pdl_wait();
+    pdl_launch_dependents();
     const int cam = blockIdx.z;
     if (stop && stop[cam]) return;
     const int tile_x = blockIdx.x / GSB_BWD_SPLIT, part = blockIdx.x % GSB_BWD_SPLIT;
@@ -674,9 +676,9 @@ void launch_raster_bwd_lift(int C, int N, int W, int H, int tile_w, int tile_h, 
                             const unsigned char* masks, const int* iso_flag, const Stripe& stripe, cudaStream_t st) {
     if (C * tile_w * tile_h == 0) return;
     dim3 grid(tile_w * GSB_BWD_SPLIT, tile_h, C);
-    raster_bwd_quad_kernel<<<grid, GSB_BWD_THREADS, 0, st>>>(C, N, W, H, tile_w, tile_h, rec, ranges, flatten_ids,
-                                                             render_alphas, last_ids, v_depth, v_alpha, means, quats,
-                                                             scales, viewmats, Ks, eps2d, partials, stop, masks, iso_flag, stripe);
+    launch_chain_kernel(raster_bwd_quad_kernel, grid, dim3(GSB_BWD_THREADS), st, C, N, W, H, tile_w, tile_h, rec, ranges,
+                        flatten_ids, render_alphas, last_ids, v_depth, v_alpha, means, quats, scales, viewmats, Ks, eps2d,
+                        partials, stop, masks, iso_flag, stripe);
 }
 
 int launch_raster_bwd_soa(int cdim, int C, int N, int W, int H, int tile_w, int tile_h, const float* means2d,

@@ -151,6 +151,8 @@ __global__ void __launch_bounds__(256) raster_fwd_pair_kernel(
     // per-warp rings of the entries that reach the warp's patch (slot pairs are 8-byte aligned)
     __shared__ __align__(8) float rx[8][64], ry[8][64], ra[8][64], rb[8][64], rc[8][64], ro[8][64], rd[8][64];
     __shared__ __align__(8) int rp[8][64];
+    pdl_wait();
+    pdl_launch_dependents();
     const int cam = blockIdx.z;
     if (stop && stop[cam]) return;
     const int tile_id = blockIdx.y * tile_w + blockIdx.x;
@@ -281,8 +283,8 @@ void launch_raster_fwd_packed(int C, int W, int H, int tile_w, int tile_h, const
                               unsigned char* masks_out, const Stripe& stripe, cudaStream_t st) {
     if (C * tile_w * tile_h == 0) return;
     dim3 grid(tile_w, tile_h, C);
-    raster_fwd_pair_kernel<<<grid, 256, 0, st>>>(W, H, tile_w, tile_h, rec, ranges, flatten_ids, render_depth,
-                                                 render_alphas, last_ids, normalize, stop, masks_out, stripe);
+    launch_chain_kernel(raster_fwd_pair_kernel, grid, dim3(256), st, W, H, tile_w, tile_h, rec, ranges, flatten_ids,
+                        render_depth, render_alphas, last_ids, normalize, stop, masks_out, stripe);
 }
 
 int launch_raster_fwd_soa(int cdim, int C, int W, int H, int tile_w, int tile_h, const float* means2d,

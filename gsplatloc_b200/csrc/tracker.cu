@@ -30,6 +30,7 @@ struct gsb_tracker {
     int N = 0, N_cap = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
+    bool pdl = true;   // programmatic dependent launch along the kernel chain (kernels.h); GSB_PDL=0 switches it off
     gsb_tracker_config cfg;
     float *means = nullptr, *quats = nullptr, *scales = nullptr, *opac = nullptr;
     float *gt = nullptr, *Ks = nullptr, *viewmats = nullptr;
@@ -63,6 +64,12 @@ struct gsb_tracker {
     cudaEvent_t stage_ev = nullptr;
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
+    // the same iteration ``graph_unroll`` times in one graph: the runs of gsb_tracker_run between two polls are launched
+    // in chunks of this many iterations (fewer graph launches; the step from pose_finish to the next projection becomes a
+    // programmatic edge as well); the one-iteration graph takes the remainder.  GSB_GRAPH_UNROLL overrides (1 = off).
+    cudaGraph_t graph_multi = nullptr;
+    cudaGraphExec_t exec_multi = nullptr;
+    int graph_unroll = 10;
     bool graph_valid = false, have_map = false, have_obs = false, have_pose = false, cap_dirty = true;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int64_t total_launches = 0;
@@ -105,6 +112,8 @@ __global__ void stripe_barrier_kernel(int world, int rank, int slot, int* own_fl
 }
 
 
+namespace gsb { thread_local bool g_pdl = false; }
+
 static const int kStages = 9;   // slots of gsb_tracker_profile; pose_begin, tile_scan and bin_emit are fused away (0)
 static int n_launches_per_iter(const gsb_tracker* t) {
     return 6 + ((t->cfg.normal_lambda != 0.f && t->cfg.normal_mode == GSB_NORMAL_REFERENCE) ? 1 : 0);
@@ -112,6 +121,9 @@ static int n_launches_per_iter(const gsb_tracker* t) {
 
 static void invalidate_graph(gsb_tracker* t) {
     if (t->exec) cudaGraphExecDestroy(t->exec);
+    if (t->exec_multi) cudaGraphExecDestroy(t->exec_multi);
+    if (t->graph_multi) cudaGraphDestroy(t->graph_multi);
+    t->exec_multi = nullptr; t->graph_multi = nullptr;
     if (t->graph) cudaGraphDestroy(t->graph);
     t->exec = nullptr; t->graph = nullptr; t->graph_valid = false;
 }
@@ -185,10 +197,14 @@ static void enqueue_segment(gsb_tracker* t, int seg, cudaEvent_t* marks, int& mk
 
 static void enqueue_iteration(gsb_tracker* t, bool forward_only, cudaEvent_t* marks = nullptr) {
     int mk = 0;
+    // one frame on one GPU, no stage marks: the kernels of the chain overlap their launch with the predecessor's tail
+    g_pdl = t->pdl && !marks && t->stripe_world <= 1 && t->n_peers == 0;
     enqueue_segment(t, 0, marks, mk);
-    if (forward_only) return;
-    enqueue_segment(t, 1, marks, mk);
-    enqueue_segment(t, 2, marks, mk);
+    if (!forward_only) {
+        enqueue_segment(t, 1, marks, mk);
+        enqueue_segment(t, 2, marks, mk);
+    }
+    g_pdl = false;
 }
 
 // (Re)allocate the fixed-capacity tile bins: keys, sorted ids and patch masks for C * tiles * tile_cap entries.
@@ -350,6 +366,8 @@ int gsb_tracker_create(gsb_tracker** out, int C, int W, int H, void* stream) {
     int dev_count = 0;
     TCK(cudaGetDeviceCount(&dev_count), "gsb_tracker_create: no CUDA device");
     gsb_tracker* t = new gsb_tracker();
+    if (const char* e = getenv("GSB_PDL")) t->pdl = atoi(e) != 0;
+    if (const char* e = getenv("GSB_GRAPH_UNROLL")) t->graph_unroll = std::min(64, std::max(1, atoi(e)));
     const int rc = tracker_alloc(t, C, W, H, stream);
     if (rc) {
         const std::string why = g_err;   // (destroy must not overwrite the reason)
@@ -466,6 +484,13 @@ static int capture_graph(gsb_tracker* t) {
     cudaError_t e = cudaStreamEndCapture(t->stream, &t->graph);
     if (e != cudaSuccess) return fail(GSB_ERR_CUDA, "end capture", e);
     TCK(cudaGraphInstantiate(&t->exec, t->graph, 0), "graph instantiate");
+    if (t->graph_unroll > 1) {
+        TCK(cudaStreamBeginCapture(t->stream, cudaStreamCaptureModeThreadLocal), "begin capture");
+        for (int u = 0; u < t->graph_unroll; ++u) enqueue_iteration(t, false);
+        e = cudaStreamEndCapture(t->stream, &t->graph_multi);
+        if (e != cudaSuccess) return fail(GSB_ERR_CUDA, "end capture", e);
+        TCK(cudaGraphInstantiate(&t->exec_multi, t->graph_multi, 0), "graph instantiate");
+    }
     t->graph_valid = true;
     return GSB_OK;
 }
@@ -492,7 +517,13 @@ int gsb_tracker_run(gsb_tracker* t, int n_iters, int poll_every, int use_graph, 
         done = 0;
         bool all_stopped = false, overflowed = false;
         for (int it = 0; it < n_iters && !all_stopped && !overflowed; ++it) {
-            if (use_graph) TCK(cudaGraphLaunch(t->exec, st), "graph launch");
+            // iterations up to the next poll (or the end) that fit the unrolled graph go in one launch
+            const int ahead = std::min(n_iters - it, poll_every > 0 ? poll_every - it % poll_every : n_iters - it);
+            if (use_graph && t->exec_multi && ahead >= t->graph_unroll) {
+                TCK(cudaGraphLaunch(t->exec_multi, st), "graph launch");
+                it += t->graph_unroll - 1;
+                done += t->graph_unroll - 1;
+            } else if (use_graph) TCK(cudaGraphLaunch(t->exec, st), "graph launch");
             else enqueue_iteration(t, false);
             ++done;
             if (poll_every > 0 && (it + 1) % poll_every == 0 && it + 1 < n_iters) {
