@@ -484,15 +484,18 @@ __global__ void __launch_bounds__(256) tile_sort_kernel(int n_tiles, int tile_bi
     }
 }
 
+// (16 KB of shared memory and 32 registers: eight blocks per SM; the shuffle rounds are latency chains, more resident
+// warps fill them.  Bins beyond 2048 keys -- three times the densest map GsplatLoc builds -- are sorted in global memory.)
+#define SORT_SMEM_FIXED 2048
 // Fixed-capacity bins (tracker path, filled by project_emit_kernel): bin b owns keys[b * tile_cap ...], cursor[b] is its
 // fill level.  Sorts the bin, publishes its range (ranges[b] = {start, start + n}: what isect_offsets[b], [b + 1] are in
 // the compact layout), re-zeroes the cursor for the next iteration and adds n to the intersection counter.
-__global__ void __launch_bounds__(256) tile_sort_fixed_kernel(int n_tiles, int tile_cap, int* __restrict__ cursor,
+__global__ void __launch_bounds__(256, 8) tile_sort_fixed_kernel(int n_tiles, int tile_cap, int* __restrict__ cursor,
                                                               uint64_t* __restrict__ keys,
                                                               int* __restrict__ flatten_ids, int2* __restrict__ ranges,
                                                               int* __restrict__ n_isects,
                                                               const int* __restrict__ stop) {
-    __shared__ uint64_t sk[SORT_SMEM];
+    __shared__ uint64_t sk[SORT_SMEM_FIXED];
     pdl_wait();
     pdl_launch_dependents();
     const int bin = blockIdx.x;
@@ -512,12 +515,12 @@ __global__ void __launch_bounds__(256) tile_sort_fixed_kernel(int n_tiles, int t
     if (n <= 512) { reg_tile_sort<2>(g, n, sk, start, flatten_ids, nullptr, 0); return; }
     if (n <= 1024) { reg_tile_sort<4>(g, n, sk, start, flatten_ids, nullptr, 0); return; }
     uint64_t* a = g;
-    if (n <= SORT_SMEM) {
+    if (n <= SORT_SMEM_FIXED) {
         for (int i = threadIdx.x; i < n; i += blockDim.x) sk[i] = g[i];
         a = sk;
     }
     __syncthreads();
-    bitonic_sort(a, n, n <= SORT_SMEM);
+    bitonic_sort(a, n, n <= SORT_SMEM_FIXED);
     for (int i = threadIdx.x; i < n; i += blockDim.x) flatten_ids[start + i] = (int)(uint32_t)a[i];
 }
 
