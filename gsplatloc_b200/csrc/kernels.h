@@ -20,9 +20,14 @@ struct Stripe {
 
 // Programmatic dependent launch for the tracker's kernel chain.  While g_pdl is set (tracker.cu: one GPU per frame, no
 // stage marks) the six kernels of an iteration are launched with the programmatic-stream-serialization attribute: a
-// kernel's blocks may be scheduled while its predecessor drains; every block executes pdl_wait() (common.cuh:
-// griddepcontrol.wait -- the predecessor has completed and its writes are visible) before it touches global memory or
-// exits, so the chain stays transitively ordered, and pdl_launch_dependents() right after lets the successor queue up.
+// kernel's blocks may be scheduled while its predecessor drains.  The rule every kernel of the chain follows:
+//   * every block executes pdl_wait() (common.cuh: griddepcontrol.wait -- the predecessor has completed and its writes
+//     are visible) before it exits, before it writes global memory and before it reads what the predecessor wrote;
+//   * pdl_launch_dependents() comes AFTER the wait.  A successor's blocks therefore start only once every block of this
+//     kernel has seen ITS predecessor complete, so the chain stays transitively ordered and a block may read, before its
+//     own wait, anything produced two or more kernels back (or constant over the loop): project_emit fetches its Gaussian
+//     while pose_finish runs, pose_finish prepares the state-dependent part of its tail during raster_bwd's last wave,
+//     raster_bwd sets up everything but the loss gradients, the loss kernel requests the observation.
 // Without the attribute both instructions do nothing.
 extern thread_local bool g_pdl;
 template <typename... KArgs, typename... Args>

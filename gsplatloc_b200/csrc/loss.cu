@@ -357,14 +357,21 @@ __global__ void __launch_bounds__(LBX* LBY) loss_track_kernel(
     __shared__ float sA[LH * LW], sB[LH * LW];
     __shared__ float sKx[(LBY + 2) * (LBX + 2)], sKy[(LBY + 2) * (LBX + 2)];
     __shared__ float s_red[2][(LBX * LBY) / 32];
-    pdl_wait();
-    pdl_launch_dependents();
     const int cam = blockIdx.z;
-    if (stop && stop[cam]) return;
     const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * LBX + tx;
     const int x0 = blockIdx.x * LBX, y0 = blockIdx.y * LBY;
     const int cam_off = cam * H * W;
     const float* d_img = ed + cam_off;
+    // the observation and its Sobel magnitude are per-frame constants: requested before the wait on the forward rasteriser
+    const int x = x0 + tx, y = y0 + ty;
+    const bool in_img = x < W && y < H;
+    const int pix_c = min(y, H - 1) * W + min(x, W - 1);
+    const int ym1 = y0 + ty - 1, xm1 = x0 + tx - 1;   // the pixel of this thread's K position (ty, tx)
+    const float pre_gt = gt[pix_c];
+    const float pre_eb = gt_edge[min(max(ym1, 0), H - 1) * W + min(max(xm1, 0), W - 1)];
+    pdl_wait();
+    pdl_launch_dependents();
+    if (stop && stop[cam]) return;
     if (!stripe_owns(2 * blockIdx.x, blockIdx.y >> 1, tile_w, stripe.rank, stripe.mask)) {
         // tile-striped frame (row f3): this 32x8 block lies in another rank's tile pair; zero partial sums keep the sum
         // over ranks exact (fused exchange: the owner stores them here itself), and nobody reads d loss / d(D, alpha) of
@@ -377,12 +384,7 @@ __global__ void __launch_bounds__(LBX* LBY) loss_track_kernel(
     const int xa = min(max(x0 + tx - 2, 0), W - 1), xb = min(x0 + tx + 30, W - 1);      // columns tx and tx + 32
     const int ya = min(max(y0 + ty - 2, 0), H - 1), yb = min(y0 + ty + 6, H - 1);       // rows ty and ty + 8
     // (everything this thread will want from global memory later is requested now: one round trip instead of three)
-    const int x = x0 + tx, y = y0 + ty;
-    const bool in_img = x < W && y < H;
-    const int pix_c = min(y, H - 1) * W + min(x, W - 1);
-    const float pre_gt = gt[pix_c], pre_al = alpha[cam_off + pix_c];
-    const int ym1 = y0 + ty - 1, xm1 = x0 + tx - 1;   // the pixel of this thread's K position (ty, tx)
-    const float pre_eb = gt_edge[min(max(ym1, 0), H - 1) * W + min(max(xm1, 0), W - 1)];
+    const float pre_al = alpha[cam_off + pix_c];
     int hole = 0;
     {
         const float d = d_img[ya * W + xa];

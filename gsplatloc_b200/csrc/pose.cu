@@ -77,12 +77,40 @@ __global__ void __cluster_dims__(GSB_POSE_CLUSTER, 1, 1) __launch_bounds__(POSE_
     float* __restrict__ history, int history_cap) {
     __shared__ float red[15][POSE_FINISH_THREADS / 32];
     __shared__ float cred[GSB_POSE_CLUSTER][16];   // written by every block of the cluster into the LEADER's copy
-    pdl_wait();
-    pdl_launch_dependents();
     cg::cluster_group cluster = cg::this_cluster();
     const int rank = (int)cluster.block_rank();
     const int c = blockIdx.x / GSB_POSE_CLUSTER, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    if (state[c].stopped) return;                  // the same answer in every block of the cluster
+    // Before the wait on raster_bwd (chain order, kernels.h): the pose state and the viewmat are what the PREVIOUS
+    // pose_finish left (six kernels back), so the part of the leader's tail that depends on them alone -- R(q), the pose
+    // errors, Adam's bias corrections -- is done while raster_bwd's last blocks are still running.
+    const bool stopped = state[c].stopped != 0;    // the same answer in every block of the cluster
+    const bool lead = rank == 0 && tid == 0;
+    float* V = viewmats + c * 16;
+    gsb_pose_state s;
+    float R[9], qn[4], qnorm = 1.f, twc[3] = {0.f, 0.f, 0.f}, eT = 0.f, eR = 0.f, bc1 = 1.f, bc2_sqrt = 1.f;
+    if (lead && !stopped) {
+        s = state[c];   // one bulk read; every update below works on the copy, one bulk write at the end
+        kornia_rotmat(s.q, R, qn, &qnorm);
+        twc[0] = V[3]; twc[1] = V[7]; twc[2] = V[11];
+        if (s.has_gt) {
+            float d0 = s.t[0] - s.gt_c2w[3], d1 = s.t[1] - s.gt_c2w[7], d2 = s.t[2] - s.gt_c2w[11];
+            eT = sqrtf(d0 * d0 + d1 * d1 + d2 * d2);
+            float tr = 0.f;  // trace(R_est R_gt^T) = sum_ij R_est[i][j] R_gt[i][j]
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+#pragma unroll
+                for (int j = 0; j < 3; ++j) tr += R[i * 3 + j] * s.gt_c2w[i * 4 + j];
+            eR = acosf(fminf(1.f, fmaxf(-1.f, (tr - 1.f) * 0.5f))) * (180.f / 3.14159265358979323846f);
+        }
+        // beta^step = 2^(step log2 beta): two exp2 / log2 pairs per iteration instead of four powf (the bias corrections
+        // agree with powf's to 1e-5 relative at beta2 = 0.999, i.e. 5e-9 of a parameter step); step = the one about to be taken
+        const float next_step = (float)(s.adam_step + 1);
+        bc1 = 1.f - exp2f(next_step * log2f(cfg.beta1));
+        bc2_sqrt = sqrtf(1.f - exp2f(next_step * log2f(cfg.beta2)));
+    }
+    pdl_wait();
+    pdl_launch_dependents();
+    if (stopped) return;
     // Distributed shared memory may only be touched once its owner block is known to run: every block arrives here and
     // waits just before its remote store below, so the barrier's latency hides behind the global-memory sums.
     cluster.barrier_arrive();
@@ -123,8 +151,7 @@ __global__ void __cluster_dims__(GSB_POSE_CLUSTER, 1, 1) __launch_bounds__(POSE_
         leader[rank * 16 + tid] = v;
     }
     cluster.sync();                                // release / acquire: the leader sees every block's 15 sums
-    if (rank != 0 || tid != 0) return;
-    gsb_pose_state s = state[c];   // one bulk read; every update below works on the copy, one bulk write at the end
+    if (!lead) return;
     float g[15];
 #pragma unroll
     for (int k = 0; k < 15; ++k) {
@@ -134,10 +161,6 @@ __global__ void __cluster_dims__(GSB_POSE_CLUSTER, 1, 1) __launch_bounds__(POSE_
         g[k] = v;
     }
     // g[0..8] = d/dR_wc (row-major), g[9..11] = d/dt_wc
-    float* V = viewmats + c * 16;
-    float R[9], qn[4], qnorm;
-    kornia_rotmat(s.q, R, qn, &qnorm);
-    float twc[3] = {V[3], V[7], V[11]};
     // d/dC = -V^T (d/dV) V^T, C = c2w:   v_R = -R (vRwc R + vtwc twc^T),  v_t = -R vtwc
     float A[9];
 #pragma unroll
@@ -166,17 +189,6 @@ __global__ void __cluster_dims__(GSB_POSE_CLUSTER, 1, 1) __launch_bounds__(POSE_
     const float Ln = (cfg.normal_lambda != 0.f && cfg.normal_mode != 0)
                          ? 1.f - g[14] * (cfg.normal_mode == 1 ? inv_pixels : inv_rows3) : 0.f;
     const float loss = cfg.depth_lambda * Ld + cfg.normal_lambda * Ln + (1.f - cfg.depth_lambda - cfg.normal_lambda) * Ls;
-    float eT = 0.f, eR = 0.f;
-    if (s.has_gt) {
-        float d0 = s.t[0] - s.gt_c2w[3], d1 = s.t[1] - s.gt_c2w[7], d2 = s.t[2] - s.gt_c2w[11];
-        eT = sqrtf(d0 * d0 + d1 * d1 + d2 * d2);
-        float tr = 0.f;  // trace(R_est R_gt^T) = sum_ij R_est[i][j] R_gt[i][j]
-#pragma unroll
-        for (int i = 0; i < 3; ++i)
-#pragma unroll
-            for (int j = 0; j < 3; ++j) tr += R[i * 3 + j] * s.gt_c2w[i * 4 + j];
-        eR = acosf(fminf(1.f, fmaxf(-1.f, (tr - 1.f) * 0.5f))) * (180.f / 3.14159265358979323846f);
-    }
     s.loss = loss; s.depth_loss = Ld; s.edge_loss = Ls; s.normal_loss = Ln; s.eT = eT; s.eR = eR;
 #pragma unroll
     for (int k = 0; k < 4; ++k) s.g_q[k] = gq[k];
@@ -212,10 +224,6 @@ __global__ void __cluster_dims__(GSB_POSE_CLUSTER, 1, 1) __launch_bounds__(POSE_
         return;  // the last gradient is discarded (break precedes optimizer_step)
     }
     s.adam_step += 1;
-    // beta^step = 2^(step log2 beta): two exp2 / log2 pairs per iteration instead of four powf (the bias corrections agree
-    // with powf's to 1e-5 relative at beta2 = 0.999, i.e. 5e-9 of a parameter step)
-    const float bc1 = 1.f - exp2f((float)s.adam_step * log2f(cfg.beta1));
-    const float bc2_sqrt = sqrtf(1.f - exp2f((float)s.adam_step * log2f(cfg.beta2)));
     adam_update(s.q, s.m_q, s.v_q, gq, 4, s.lr_q, cfg.wd_quat, cfg.beta1, cfg.beta2, cfg.adam_eps, bc1, bc2_sqrt);
     adam_update(s.t, s.m_t, s.v_t, vt, 3, s.lr_t, cfg.wd_trans, cfg.beta1, cfg.beta2, cfg.adam_eps, bc1, bc2_sqrt);
     s.lr_q *= cfg.lr_gamma;

@@ -199,7 +199,7 @@ void launch_project_bwd(int C, int N, const float* means, const float* quats, co
 // would overflow raises *overflow (the run is reported invalid and re-sized, tracker.cu).  Thread (0,0) clears the
 // intersection counter that tile_sort accumulates.
 template <bool STRIPED>
-__global__ void __launch_bounds__(256) project_emit_kernel(
+__global__ void __launch_bounds__(256, 6) project_emit_kernel(
     int C, int N, const float* __restrict__ means, const float* __restrict__ quats, const float* __restrict__ scales,
     const float* __restrict__ opacities, const float* __restrict__ viewmats, const float* __restrict__ Ks, int W, int H,
     int tile_w, int tile_h, float eps2d, float near_plane, float far_plane, float radius_clip,
@@ -210,10 +210,15 @@ __global__ void __launch_bounds__(256) project_emit_kernel(
     // only into the tiles it owns (common.cuh stripe_owns; stripe_mask = world - 1, 0 = one GPU: every tile).  The
     // records are written for every Gaussian either way.
     __shared__ int s_incl[8][32];
-    pdl_wait();
-    pdl_launch_dependents();
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     const int c = blockIdx.y;
+    // The map never changes inside the loop: its Gaussian is fetched BEFORE the wait, i.e. while the predecessor in the chain
+    // (pose_finish of the previous iteration, eight blocks on an otherwise empty GPU) is still running.
+    GaussIn g;
+    float opac = 0.f;
+    if (n < N) { g = load_gauss(means, quats, scales, n); opac = opacities[n]; }
+    pdl_wait();
+    pdl_launch_dependents();
     if (n == 0 && c == 0) *n_isects = 0;
     if (stop && stop[c]) return;   // uniform over the block
     const int lane = threadIdx.x & 31;
@@ -223,12 +228,11 @@ __global__ void __launch_bounds__(256) project_emit_kernel(
     const size_t i = (size_t)c * N + (n < N ? n : 0);
     if (n < N) {
         Cam cam = load_cam(viewmats + c * 16, Ks + c * 9);
-        GaussIn g = load_gauss(means, quats, scales, n);
         Proj p; float S[6], Sc[6];
         const bool ok = project_gaussian(cam, g.mean, g.q, g.s, W, H, eps2d, near_plane, far_plane, radius_clip, p, S, Sc);
         if (ok) {
             tile_bbox(p.mx, p.my, p.radius, GSB_TILE, tile_w, tile_h, x0, y0, x1, y1);
-            rec[2 * i] = make_float4(p.mx, p.my, p.pz, opacities[n]);
+            rec[2 * i] = make_float4(p.mx, p.my, p.pz, opac);
             rec[2 * i + 1] = make_float4(p.ca, p.cb, p.cc, __int_as_float(p.radius));
             depth = p.pz;
             live = x1 > x0 && y1 > y0;

@@ -396,10 +396,11 @@ __global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad_
     __shared__ float s_pose[12 * GSB_BWD_THREADS];
     __shared__ LiftCtx s_ctxs[GSB_BWD_WARPS];   // one copy per warp: no block barrier before the loop
 
-    pdl_wait();
-    pdl_launch_dependents();
+    // Chain order (kernels.h): only d loss / d(depth, alpha) comes from the predecessor (the loss kernel); everything else
+    // this block sets up -- camera, ranges, the forward's alpha / last ids, the first record gather -- was written by
+    // kernels the predecessor itself waited for, so it is read before the wait and overlaps the predecessor's tail.
     const int cam = blockIdx.z;
-    if (stop && stop[cam]) return;
+    if (stop && stop[cam]) { pdl_wait(); return; }
     const int tile_x = blockIdx.x / GSB_BWD_SPLIT, part = blockIdx.x % GSB_BWD_SPLIT;
     const int tile_id = blockIdx.y * tile_w + tile_x;
     const int tid = threadIdx.x, lane = tid & 31, lwid = tid >> 5;
@@ -412,6 +413,7 @@ __global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad_
     if (!stripe_owns(tile_x, blockIdx.y, tile_w, stripe.rank, stripe.mask)) {
         // tile-striped frame (row f3): another rank replays this tile.  A zero partial keeps the sum over ranks exact; with
         // the fused exchange the owner stores the partial into this rank's buffer itself.
+        pdl_wait();
         if (tid < 12 && stripe.n_peers == 0) partials[((size_t)bin * GSB_BWD_SPLIT + part) * 12 + tid] = 0.f;
         return;
     }
@@ -446,10 +448,8 @@ __global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad_
         const int i = i0 + r;
         const bool inside = (i < H) && (j < W);
         const size_t pix = ((size_t)cam * H + min(i, H - 1)) * W + min(j, W - 1);
-        const float Tf = inside ? 1.f - render_alphas[pix] : 1.f;
-        T[r] = Tf; nbuf[r] = 0.f;
-        v_rc[r] = inside ? v_depth[pix] : 0.f;
-        v_raT[r] = inside ? Tf * v_alpha_img[pix] : 0.f;
+        T[r] = inside ? 1.f - render_alphas[pix] : 1.f;
+        nbuf[r] = 0.f;
         bin_final[r] = inside ? last_ids[pix] : -1;
         warp_bin_final = max(warp_bin_final, bin_final[r]);
     }
@@ -490,6 +490,16 @@ __global__ void __launch_bounds__(GSB_BWD_THREADS, GSB_BWD_OCC) raster_bwd_quad_
         if (top - lane >= range_start) { nxt_m = masks[top - lane]; nxt_g = flatten_ids[top - lane]; }
         issue_records(top);
         if (top - 32 - lane >= range_start) { nxt_m = masks[top - 32 - lane]; nxt_g = flatten_ids[top - 32 - lane]; }
+    }
+    pdl_wait();     // the loss kernel has finished: its gradients of the lane's four pixels
+    pdl_launch_dependents();
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const int i = i0 + r;
+        const bool inside = (i < H) && (j < W);
+        const size_t pix = ((size_t)cam * H + min(i, H - 1)) * W + min(j, W - 1);
+        v_rc[r] = inside ? v_depth[pix] : 0.f;
+        v_raT[r] = inside ? T[r] * v_alpha_img[pix] : 0.f;
     }
     __syncwarp();   // the lift context written by lane 0
     while (more || r_tail - r_head > 0) {
