@@ -150,6 +150,56 @@ def test_graph_and_eager_are_identical_and_deterministic(gsb):
     assert np.array_equal(outs[1].view(np.uint32), outs[2].view(np.uint32))
 
 
+def test_unrolled_chained_graph_is_bit_identical_to_plain_launches(gsb, monkeypatch):
+    """gsb_tracker_run replays ten iterations per graph launch between two polls, the kernels chained by programmatic
+    dependent launch (kernels.h).  27 iterations = two ten-iteration graphs + seven single ones; against eager launches,
+    against GSB_PDL=0 (plain stream order) and against GSB_GRAPH_UNROLL=1 (one iteration per graph): the same bits, the
+    same iteration counts.  The frame is small on purpose: every kernel of an iteration fits the GPU at once, the case in
+    which a wrongly ordered chain would let a block read what its grand-predecessor is still writing."""
+    fp = U.frame(U.SMALL_CAM, stride=2, seed=21)
+    c2w0 = _start_pose(fp)
+
+    def run(use_graph, env):
+        for k in ("GSB_PDL", "GSB_GRAPH_UNROLL"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        trk = _tracker(gsb, fp, c2w0, fp.src_depth, early_stop=False)     # (the switches are read at creation)
+        out = trk.run(27, poll_every=0, use_graph=use_graph)
+        st = trk.states()[0]
+        trk.close()
+        assert out["iters"] == 27 and st["iter"] == 27
+        return np.concatenate([st["q"], st["t"], st["g_q"], st["g_t"], [st["loss"]]]).astype(np.float32).view(np.uint32)
+
+    ref = run(False, {"GSB_PDL": "0"})
+    for use_graph, env in ((True, {}), (False, {}), (True, {"GSB_PDL": "0"}), (True, {"GSB_GRAPH_UNROLL": "1"}),
+                           (True, {"GSB_GRAPH_UNROLL": "4"})):
+        assert np.array_equal(run(use_graph, env), ref), (use_graph, env)
+
+
+def test_early_stop_inside_an_unrolled_graph_stops_at_the_same_iteration(gsb, monkeypatch):
+    """The stop flag is raised on the device in the middle of a ten-iteration graph: the remaining iterations of the graph
+    are no-ops, and the pose, the best pose and the iteration counter equal those of one-iteration graphs polled every
+    iteration."""
+    fp = U.frame(U.SMALL_CAM, stride=2, seed=17, trans_cm=0.5, rot_deg=0.2)
+    outs = []
+    for env, poll in (({"GSB_GRAPH_UNROLL": "1"}, 1), ({}, 0)):
+        monkeypatch.delenv("GSB_GRAPH_UNROLL", raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        # (large learning rates make the loss oscillate so that the patience rule fires early)
+        trk = _tracker(gsb, fp, fp.tar_c2w, fp.src_depth, max_steps=300, early_stop=True, patience=12, warmup=10,
+                       trans_lr=2e-2, quat_lr=1e-2)
+        trk.run(300, poll_every=poll, use_graph=True)
+        st = trk.states()[0]
+        trk.close()
+        outs.append((st["stopped"], st["iter"], st["best_iter"],
+                     np.concatenate([st["q"], st["t"], st["best_q"], st["best_t"]]).astype(np.float32).view(np.uint32)))
+    assert outs[0][0] == 1 and outs[0][1] < 300, outs[0][:3]         # it did stop early
+    assert outs[0][:3] == outs[1][:3]
+    assert np.array_equal(outs[0][3], outs[1][3])
+
+
 def test_converges_to_ground_truth_pose(gsb):
     """Converged ATE within 1e-3 m of the known synthetic delta (BASELINE.json north_star)."""
     fp = U.frame(U.MID_CAM, stride=1, seed=31, trans_cm=1.5, rot_deg=0.7)
