@@ -181,8 +181,11 @@ int gsb_tracker_set_observation(gsb_tracker* t, const float* depth, int on_host,
  * learning rates and early-stop state (a fresh CameraOptModule_quat_tans, gs_trainer_total.py:63-72). */
 int gsb_tracker_set_poses(gsb_tracker* t, const float* c2w_init_host, const float* c2w_gt_host);
 /* Run up to n_iters iterations (all cameras in lock-step; a camera whose early stop fired is frozen).
- * poll_every: how often the host looks at the stop flags (0: only at the end).  use_graph: replay a CUDA graph
- * of one iteration.  *iters_done: iterations launched; *elapsed_ms (nullable): device time by CUDA events. */
+ * poll_every: how often the host looks at the stop flags (0: only at the end).  use_graph: replay CUDA graphs of the
+ * iteration (ten iterations per launch between two polls, one per launch for the remainder; the kernels are chained by
+ * programmatic dependent launch; environment GSB_GRAPH_UNROLL=1 / GSB_PDL=0, read by gsb_tracker_create, switch either
+ * off; results are bit-identical either way).  *iters_done: iterations launched; *elapsed_ms (nullable): device time by
+ * CUDA events. */
 int gsb_tracker_run(gsb_tracker* t, int n_iters, int poll_every, int use_graph, int* iters_done, float* elapsed_ms);
 int gsb_tracker_get_states(gsb_tracker* t, gsb_pose_state* out_host);
 /* last forward: depth[C,H,W] (expected depth "ED"), alpha[C,H,W]; either may be NULL; on_host selects D2H */
