@@ -151,6 +151,23 @@ __device__ __forceinline__ bool project_gaussian(const Cam& cam, const float* __
     return p.radius > 0;
 }
 
+// The same for an isotropic Gaussian (sx == sy == sz = s): Sigma = Rq (s^2 I) Rq^T = s^2 I for any quaternion, and
+// R Sigma R^T = s^2 I in the camera frame for any pose, so the quaternion and both 3x3 congruences drop out (GsplatLoc's
+// maps: one KNN distance repeated three times, geometry.py:44-66; the backward's lift takes the same short cut).
+__device__ __forceinline__ bool project_gaussian_iso(const Cam& cam, const float* __restrict__ mean, float s, int W, int H,
+                                                     float eps2d, float near_plane, float far_plane, float radius_clip,
+                                                     Proj& p) {
+    p.px = cam.R[0] * mean[0] + cam.R[1] * mean[1] + cam.R[2] * mean[2] + cam.t[0];
+    p.py = cam.R[3] * mean[0] + cam.R[4] * mean[1] + cam.R[5] * mean[2] + cam.t[1];
+    p.pz = cam.R[6] * mean[0] + cam.R[7] * mean[1] + cam.R[8] * mean[2] + cam.t[2];
+    p.radius = 0;
+    if (p.pz < near_plane || p.pz > far_plane) return false;
+    const float s2 = s * s;
+    const float Sc[6] = {s2, 0.f, 0.f, s2, 0.f, s2};
+    persp_project(cam, Sc, W, H, eps2d, radius_clip, p);
+    return p.radius > 0;
+}
+
 // A.3 tile bounding box (fp32 exactly as the reference kernel; (u32) of a negative float saturates to 0).
 __device__ __forceinline__ void tile_bbox(float mx, float my, int radius, int tile_size, int tile_w, int tile_h,
                                           uint32_t& x0, uint32_t& y0, uint32_t& x1, uint32_t& y1) {

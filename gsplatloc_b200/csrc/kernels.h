@@ -59,7 +59,7 @@ void launch_project_emit(int C, int N, const float* means, const float* quats, c
                          const float* opacities, const float* viewmats, const float* Ks, int W, int H, int tile_w,
                          int tile_h, float eps2d, float near_plane, float far_plane, float radius_clip, float4* rec,
                          int* cursor, uint64_t* keys, int tile_cap, int* n_isects, int* overflow, const int* stop,
-                         int stripe_rank, int stripe_world, cudaStream_t st);
+                         int stripe_rank, int stripe_world, const int* iso_flag, cudaStream_t st);
 
 // ---- isect.cu
 void launch_isect_count(int CN, const float* means2d, const int* radii, int tile_size, int tile_w, int tile_h,

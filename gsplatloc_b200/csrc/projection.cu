@@ -205,7 +205,7 @@ __global__ void __launch_bounds__(256, 6) project_emit_kernel(
     int tile_w, int tile_h, float eps2d, float near_plane, float far_plane, float radius_clip,
     float4* __restrict__ rec, int* __restrict__ cursor, uint64_t* __restrict__ keys, int tile_cap,
     int* __restrict__ n_isects, int* __restrict__ overflow, const int* __restrict__ stop, int stripe_rank,
-    int stripe_mask) {
+    int stripe_mask, const int* __restrict__ iso_flag) {
     // Tile-striped single frame over several GPUs: every rank projects all Gaussians but bins
     // only into the tiles it owns (common.cuh stripe_owns; stripe_mask = world - 1, 0 = one GPU: every tile).  The
     // records are written for every Gaussian either way.
@@ -217,6 +217,7 @@ __global__ void __launch_bounds__(256, 6) project_emit_kernel(
     GaussIn g;
     float opac = 0.f;
     if (n < N) { g = load_gauss(means, quats, scales, n); opac = opacities[n]; }
+    const bool iso = iso_flag ? (*iso_flag != 0) : false;   // set with the map (tracker.cu map_iso_kernel)
     pdl_wait();
     pdl_launch_dependents();
     if (n == 0 && c == 0) *n_isects = 0;
@@ -229,7 +230,8 @@ __global__ void __launch_bounds__(256, 6) project_emit_kernel(
     if (n < N) {
         Cam cam = load_cam(viewmats + c * 16, Ks + c * 9);
         Proj p; float S[6], Sc[6];
-        const bool ok = project_gaussian(cam, g.mean, g.q, g.s, W, H, eps2d, near_plane, far_plane, radius_clip, p, S, Sc);
+        const bool ok = iso ? project_gaussian_iso(cam, g.mean, g.s[0], W, H, eps2d, near_plane, far_plane, radius_clip, p)
+                            : project_gaussian(cam, g.mean, g.q, g.s, W, H, eps2d, near_plane, far_plane, radius_clip, p, S, Sc);
         if (ok) {
             tile_bbox(p.mx, p.my, p.radius, GSB_TILE, tile_w, tile_h, x0, y0, x1, y1);
             rec[2 * i] = make_float4(p.mx, p.my, p.pz, opac);
@@ -323,17 +325,17 @@ void launch_project_emit(int C, int N, const float* means, const float* quats, c
                          const float* opacities, const float* viewmats, const float* Ks, int W, int H, int tile_w,
                          int tile_h, float eps2d, float near_plane, float far_plane, float radius_clip, float4* rec,
                          int* cursor, uint64_t* keys, int tile_cap, int* n_isects, int* overflow, const int* stop,
-                         int stripe_rank, int stripe_world, cudaStream_t st) {
+                         int stripe_rank, int stripe_world, const int* iso_flag, cudaStream_t st) {
     if (N == 0 || C == 0) return;
     dim3 grid((N + 255) / 256, C);
     if (stripe_world > 1)
         launch_chain_kernel(project_emit_kernel<true>, grid, dim3(256), st, C, N, means, quats, scales, opacities, viewmats,
                             Ks, W, H, tile_w, tile_h, eps2d, near_plane, far_plane, radius_clip, rec, cursor, keys,
-                            tile_cap, n_isects, overflow, stop, stripe_rank, stripe_world - 1);
+                            tile_cap, n_isects, overflow, stop, stripe_rank, stripe_world - 1, iso_flag);
     else
         launch_chain_kernel(project_emit_kernel<false>, grid, dim3(256), st, C, N, means, quats, scales, opacities, viewmats,
                             Ks, W, H, tile_w, tile_h, eps2d, near_plane, far_plane, radius_clip, rec, cursor, keys,
-                            tile_cap, n_isects, overflow, stop, 0, 0);
+                            tile_cap, n_isects, overflow, stop, 0, 0, iso_flag);
 }
 
 void launch_project_bin(int C, int N, const float* means, const float* quats, const float* scales,

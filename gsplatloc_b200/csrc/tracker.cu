@@ -165,7 +165,7 @@ static void enqueue_segment(gsb_tracker* t, int seg, cudaEvent_t* marks, int& mk
         // projection + scatter into fixed-capacity tile bins in ONE pass (no histogram, scan or second pass)
         launch_project_emit(C, N, t->means, t->quats, t->scales, t->opac, t->viewmats, t->Ks, t->W, t->H, t->tile_w,
                             t->tile_h, c.eps2d, c.near_plane, c.far_plane, c.radius_clip, t->rec, t->cursor, t->keys,
-                            t->tile_cap, t->n_isects, t->overflow, t->stop, t->stripe_rank, t->stripe_world, st);
+                            t->tile_cap, t->n_isects, t->overflow, t->stop, t->stripe_rank, t->stripe_world, t->iso_flag, st);
         GSB_MARK();
         GSB_MARK();   // (tile_scan slot)
         GSB_MARK();   // (bin_emit slot)
